@@ -1,0 +1,145 @@
+/* sbx.h -- C ABI of libsimubox_b200.so: B200 (sm_100a) density-field analysis hot path.
+ *
+ * The reference (KangruiYuan/SimuBox) has no FFI for this path -- it is plain Python
+ * (SURVEY.md 8(b)).  Each entry point below names the reference code it replaces; the
+ * Python layer (simubox_b200/scatter.py, voronoi.py) binds them with ctypes and keeps the
+ * reference's call signatures.  INTEGRATION.md shows the stub a SimuBox maintainer adds.
+ *
+ * Conventions
+ *   - return 0 (SBX_OK) or a negative SBX_E* code; text via sbx_last_error() (thread-local).
+ *   - pointers are CUDA DEVICE pointers unless the name ends in _host / the comment says host.
+ *   - the library never allocates caller-visible buffers; a plan owns its cuFFT workspace,
+ *     tables and scratch.  A plan is bound to one device and is not thread-safe.
+ *   - *_execute calls are asynchronous on `stream` (a cudaStream_t passed as void*; NULL =
+ *     legacy default stream) and never synchronise, except the *_host variants which
+ *     return after the results are in host memory.
+ *   - no CPU fallback: without an sm_100 device plan creation fails with SBX_ENODEVICE.
+ */
+#ifndef SBX_H
+#define SBX_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SBX_VERSION 100 /* 0.1.0 */
+
+enum {
+  SBX_OK = 0,
+  SBX_EINVAL = -1,    /* bad argument (odd grid size, ndim, NULL pointer ...)          */
+  SBX_ENODEVICE = -2, /* no CUDA device / not compute capability 10.x                   */
+  SBX_ECUDA = -3,     /* CUDA runtime error                                             */
+  SBX_ECUFFT = -4,    /* cuFFT error                                                    */
+  SBX_ENOMEM = -5,    /* host or device allocation failed                               */
+  SBX_ENCCL = -6,     /* NCCL error / NCCL library not loadable                         */
+  SBX_ERANGE = -7     /* output capacity too small (max_peaks, member buffer ...)        */
+};
+
+/* device = SBX_DEVICE_NONE builds a geometry-only scatter plan on the host (shell table,
+ * q, counts, members); no CUDA call is made and the *_execute entry points return
+ * SBX_ENODEVICE.  Used to inspect the shell geometry and by the CPU-side tests. */
+#define SBX_DEVICE_NONE (-1)
+
+/* scatter-plan flags (sbx_scatter_plan_create_ex) */
+enum {
+  SBX_SCATTER_AUTO = 0,       /* choose the fastest valid path                                */
+  SBX_SCATTER_FFT_DENSE = 1,  /* cuFFT D2Z + fused full-spectrum |F|^2/shell-histogram kernel */
+  SBX_SCATTER_FFT_GATHER = 2, /* cuFFT D2Z + fused gather of the shell members only           */
+  SBX_SCATTER_PRUNED = 3      /* hand-written pruned DFT of the member modes (no spectrum)    */
+};
+
+typedef struct sbx_scatter_plan sbx_scatter_plan;
+typedef struct sbx_slab_plan sbx_slab_plan;
+
+int sbx_version(void);
+const char* sbx_last_error(void);
+/* number of visible CUDA devices with compute capability 10.x; <0 on error */
+int sbx_device_count(void);
+
+/* ---- scattering: replaces Scatter.k_space + Scatter.sacttering_peak -----------------
+ * (reference SimuBox/calculator/scatter.py:40-65 and :68-122).
+ * ndim in 1..3; N[d] even; L[d] box lengths; cutoff/threshold as in sacttering_peak.
+ * Builds: k^2 component tables (scatter.py:60), the field-independent shell table that the
+ * reference obtains by argsort + merge loop (scatter.py:97-115, incl. the meshgrid 'xy'
+ * pairing of :62-63 and the truncated last shell of :106-107), cuFFT D2Z plan(s) for up to
+ * max_batch fields per launch. */
+int sbx_scatter_plan_create(sbx_scatter_plan** out, int device, int ndim, const int64_t* N,
+                            const double* L, int cutoff, double threshold, int max_batch);
+int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, int ndim, const int64_t* N,
+                               const double* L, int cutoff, double threshold, int max_batch,
+                               int path /* SBX_SCATTER_* */);
+int sbx_scatter_plan_destroy(sbx_scatter_plan* plan);
+
+/* Geometry of the result rows = q_Intensity[:,0] and member counts (scatter.py:117-118).
+ * q_host / count_host may be NULL to query n_shells only.  Host pointers. */
+int sbx_scatter_plan_shells(const sbx_scatter_plan* plan, int* n_shells, double* q_host,
+                            int64_t* count_host);
+/* q_idx[shell] (scatter.py:103,110-115): n member vectors of ndim squared k components each,
+ * in ascending spectrum-index order.  Pass k2xyz_host = NULL to query n.  Host pointers. */
+int sbx_scatter_plan_members(const sbx_scatter_plan* plan, int shell, int64_t* n,
+                             double* k2xyz_host, int64_t capacity);
+/* which SBX_SCATTER_* path the plan runs */
+int sbx_scatter_plan_path(const sbx_scatter_plan* plan);
+
+/* fields: batch x prod(N) fp64, C order (= DensityParseResult.mat of each field);
+ * shell_I: batch x n_shells fp64 = q_Intensity[:,1] per field.  batch <= max_batch. */
+int sbx_scatter_execute(sbx_scatter_plan* plan, const double* fields, int batch, double* shell_I,
+                        void* stream);
+
+/* ---- peaks: replaces the numeric part of Scatter.show_peak (scatter.py:137-149) and
+ * peak.gaussian_expansion (calculator/peak.py:11-17) + scipy.signal.find_peaks(height=).
+ * q: n shell positions (shared by the batch); I: batch x n intensities (row 0 is zeroed
+ * internally, scatter.py:138); rows with q <= q_cutoff are kept (:141).
+ * plot_y: batch x step; peak_idx: batch x max_peaks ascending sample indices;
+ * n_peaks: batch counts (may exceed max_peaks: then only the first max_peaks are stored). */
+int sbx_peaks_execute(const double* q, const double* I, int n, int batch, double width, int step,
+                      double q_cutoff, double min_height, double* plot_y, int32_t* peak_idx,
+                      int32_t* n_peaks, int max_peaks, void* stream);
+
+/* scatter + peaks in one call (the fused tail runs in the last-arriving block of each field) */
+int sbx_scatter_peaks_execute(sbx_scatter_plan* plan, const double* fields, int batch,
+                              double* shell_I, double width, int step, double q_cutoff,
+                              double min_height, double* plot_y, int32_t* peak_idx,
+                              int32_t* n_peaks, int max_peaks, void* stream);
+
+/* End-to-end variant with HOST buffers (pinned memory recommended): total fields are
+ * streamed through the plan in chunks of max_batch with copy/compute overlap; returns after
+ * shell_I_host (total x n_shells) -- and, if non-NULL, peak_idx_host / n_peaks_host -- are
+ * complete.  This is the call Scatter.sacttering_peak_batch makes. */
+int sbx_scatter_execute_host(sbx_scatter_plan* plan, const double* fields_host, int64_t total,
+                             double* shell_I_host, double width, int step, double q_cutoff,
+                             double min_height, int32_t* peak_idx_host, int32_t* n_peaks_host,
+                             int max_peaks);
+
+/* ---- Voronoi labelling: replaces the per-pixel loop of
+ * VoronoiCell.weighted_voronoi_diagrams (calculator/voronoi.py:284-292) with
+ * VoronoiCell.additive (:244-246, mode 0) or VoronoiCell.power (:249-255, mode 1).
+ * ndim 2 or 3; N grid size; seeds S x ndim fp64 (voxel units); weights S fp64 or NULL (= 0);
+ * box_host: ndim periodic lengths on the HOST or NULL for the reference's non-periodic
+ * behaviour; mask: prod(N) uint8 or NULL (voxels with mask == 0 get label -1);
+ * labels: prod(N) int32, C order (x-major like product(range(imgx), range(imgy))).
+ * Ties go to the lowest seed index (np.argmin).  stats_host (may be NULL) receives
+ * [distance evaluations, tiles, overflowed tiles] after a stream sync when non-NULL. */
+int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
+                      const double* weights, int mode, const double* box_host,
+                      const uint8_t* mask, int32_t* labels, void* stream, int64_t* stats_host);
+
+/* ---- one giant field across GPUs: slab-decomposed FFT + NCCL all-to-all ---------------
+ * nccl_comm: an ncclComm_t (as void*) spanning `world` ranks; local_slab = planes
+ * [rank*N0/world, (rank+1)*N0/world) of the field; shell_I: n_shells fp64, identical on all
+ * ranks after the call completes on `stream`. */
+int sbx_scatter_slab_plan_create(sbx_slab_plan** out, void* nccl_comm, int rank, int world,
+                                 int device, const int64_t* N, const double* L, int cutoff,
+                                 double threshold);
+int sbx_scatter_slab_shells(const sbx_slab_plan* plan, int* n_shells, double* q_host,
+                            int64_t* count_host);
+int sbx_scatter_slab_execute(sbx_slab_plan* plan, const double* local_slab, double* shell_I,
+                             void* stream);
+int sbx_scatter_slab_plan_destroy(sbx_slab_plan* plan);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SBX_H */

@@ -1,0 +1,480 @@
+// scatter.cu -- scatter plan + C ABI (see include/sbx.h).  cuFFT D2Z is a stated library call;
+// everything after the transform is the hand-written kernels of scatter_kernels.cuh.
+#include <cufft.h>
+
+#include <algorithm>
+#include <cmath>
+#include <cstdlib>
+#include <cstring>
+#include <map>
+#include <new>
+#include <vector>
+
+#include "common.h"
+#include "scatter_kernels.cuh"
+#include "shell_table.h"
+
+namespace sbx {
+
+thread_local char g_err[512] = "";
+char* last_error_buf() { return g_err; }
+
+int require_sm100(int device) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess || n == 0) {
+    cudaGetLastError();
+    return fail(SBX_ENODEVICE, "no CUDA device visible (this library has no CPU fallback)");
+  }
+  if (device < 0 || device >= n) return fail(SBX_ENODEVICE, "device %d out of range (%d visible)", device, n);
+  int major = 0;
+  cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, device);
+  if (major != 10) return fail(SBX_ENODEVICE, "device %d has compute capability %d.x; sm_100 required", device, major);
+  return SBX_OK;
+}
+
+#define SBX_CUFFT(call)                                                                       \
+  do {                                                                                        \
+    cufftResult r_ = (call);                                                                  \
+    if (r_ != CUFFT_SUCCESS) return ::sbx::fail(SBX_ECUFFT, "%s:%d %s -> cufftResult %d", __FILE__, __LINE__, #call, (int)r_); \
+  } while (0)
+
+template <class T>
+static int upload(T** dptr, const std::vector<T>& h) {
+  *dptr = nullptr;
+  if (h.empty()) return SBX_OK;
+  SBX_CUDA(cudaMalloc((void**)dptr, h.size() * sizeof(T)));
+  SBX_CUDA(cudaMemcpy(*dptr, h.data(), h.size() * sizeof(T), cudaMemcpyHostToDevice));
+  return SBX_OK;
+}
+
+}  // namespace sbx
+
+using namespace sbx;
+
+struct sbx_scatter_plan {
+  int device = 0;
+  int path = SBX_SCATTER_FFT_DENSE;
+  int max_batch = 1;
+  int chunk = 1;  // fields per cuFFT launch (spectrum workspace = chunk fields)
+  ShellTable tab;
+  GridDev grid{};
+  ShellDev shell{};
+  std::vector<double> q_host;
+  // device tables
+  double* d_rep = nullptr;
+  double* d_q = nullptr;
+  double2* d_plane2 = nullptr;
+  double* d_plane = nullptr;
+  double* d_kvlast = nullptr;
+  long long* d_elem = nullptr;
+  int* d_shell_off = nullptr;
+  unsigned int* d_tickets = nullptr;
+  double2* d_spec = nullptr;
+  std::map<int, cufftHandle> fft;  // batch -> plan
+  int blocks_per_field = 1;
+  int sm_count = 148;
+  // host-streaming state (sbx_scatter_execute_host)
+  cudaStream_t s_copy = nullptr, s_comp = nullptr;
+  double* d_stage[2] = {nullptr, nullptr};
+  double* d_out[2] = {nullptr, nullptr};
+  int32_t* d_pidx[2] = {nullptr, nullptr};
+  int32_t* d_npk[2] = {nullptr, nullptr};
+  int stage_max_peaks = 0;
+  cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+};
+
+static int get_fft(sbx_scatter_plan* p, int batch, cufftHandle* out) {
+  auto it = p->fft.find(batch);
+  if (it != p->fft.end()) { *out = it->second; return SBX_OK; }
+  cufftHandle h;
+  int n[3];
+  for (int d = 0; d < p->tab.ndim; ++d) n[d] = (int)p->tab.N[d];
+  SBX_CUFFT(cufftCreate(&h));
+  size_t ws = 0;
+  SBX_CUFFT(cufftMakePlanMany(h, p->tab.ndim, n, nullptr, 1, 0, nullptr, 1, 0, CUFFT_D2Z, batch, &ws));
+  p->fft[batch] = h;
+  *out = h;
+  return SBX_OK;
+}
+
+static void fill_q(sbx_scatter_plan* p) {
+  const ShellTable& t = p->tab;
+  p->q_host.resize(t.n_shells());
+  for (int s = 0; s < t.n_shells(); ++s) p->q_host[s] = std::sqrt(t.rep[s]);  // scatter.py:118
+}
+
+static int build_device_tables(sbx_scatter_plan* p) {
+  const ShellTable& t = p->tab;
+  GridDev& g = p->grid;
+  g.ndim = t.ndim;
+  g.N0 = (int)t.N[0]; g.N1 = (int)t.N[1]; g.N2 = (int)t.N[2];
+  const int64_t nlast = t.N[t.ndim - 1];
+  g.H = (int)(nlast / 2 + 1);
+  g.nreal = t.total();
+  g.nspec = g.nreal / nlast * g.H;
+  g.factor = 1.0 / (double)g.nreal;
+  int rc;
+  if (t.ndim == 3) {
+    const int64_t rows = t.N[0] * t.N[1];
+    std::vector<double2> p2(rows);
+    for (int64_t row = 0; row < rows; ++row) {
+      const int64_t a = row / t.N[1], b = row % t.N[1];
+      const int64_t mrow = (a ? t.N[0] - a : 0) * t.N[1] + (b ? t.N[1] - b : 0);
+      volatile double x = t.kv[0][row % t.N[0]] + t.kv[1][row / t.N[0]];
+      volatile double y = t.kv[0][mrow % t.N[0]] + t.kv[1][mrow / t.N[0]];
+      p2[row] = make_double2(x, y);
+    }
+    if ((rc = upload(&p->d_plane2, p2))) return rc;
+    std::vector<double> kl(t.kv[2].begin(), t.kv[2].begin() + g.H);
+    if ((rc = upload(&p->d_kvlast, kl))) return rc;
+  } else {
+    std::vector<double> pl(t.total());
+    for (int64_t f = 0; f < t.total(); ++f) pl[f] = t.k2_of(f);
+    if ((rc = upload(&p->d_plane, pl))) return rc;
+  }
+  g.plane2 = p->d_plane2; g.plane = p->d_plane; g.kvlast = p->d_kvlast;
+
+  if ((rc = upload(&p->d_rep, t.rep))) return rc;
+  if ((rc = upload(&p->d_q, p->q_host))) return rc;
+  ShellDev& sh = p->shell;
+  sh.rep = p->d_rep;
+  sh.n_shells = t.n_shells();
+  sh.truncated = t.truncated ? 1 : 0;
+  sh.designated = t.designated;
+  sh.threshold = t.threshold;
+  // Anything above vcut fails |rep_last - v| <= threshold with margin (pre-filter only; the exact
+  // reference comparison is repeated in shell_of()).
+  const double top = t.rep.back() + t.threshold;
+  sh.vcut = top + 8.0 * std::fabs(top) * 2.220446049250313e-16 + 1e-300;
+
+  // gather list: members -> stored element (direct, or the Hermitian mirror if c > N_last/2)
+  std::vector<long long> elem;
+  std::vector<int> off(1, 0);
+  elem.reserve((size_t)t.n_members());
+  for (int s = 0; s < t.n_shells(); ++s) {
+    for (int64_t f : t.members[s]) {
+      int64_t c = f % nlast;
+      int64_t src = f;
+      if (c > nlast / 2) { src = t.mirror_of(f); c = src % nlast; }
+      elem.push_back((src / nlast) * g.H + c);
+    }
+    off.push_back((int)elem.size());
+  }
+  if ((rc = upload(&p->d_elem, elem))) return rc;
+  if ((rc = upload(&p->d_shell_off, off))) return rc;
+  return SBX_OK;
+}
+
+extern "C" int sbx_version(void) { return SBX_VERSION; }
+extern "C" const char* sbx_last_error(void) { return g_err; }
+
+extern "C" int sbx_device_count(void) {
+  int n = 0;
+  if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+  int ok = 0;
+  for (int d = 0; d < n; ++d) {
+    int major = 0;
+    cudaDeviceGetAttribute(&major, cudaDevAttrComputeCapabilityMajor, d);
+    ok += (major == 10);
+  }
+  return ok;
+}
+
+// ------------------------------------------------------------------------------ plan life cycle
+static void free_plan(sbx_scatter_plan* p) {
+  if (!p) return;
+  if (p->device == SBX_DEVICE_NONE) { delete p; return; }
+  DeviceGuard guard(p->device);
+  for (auto& kv : p->fft) cufftDestroy(kv.second);
+  cudaFree(p->d_rep); cudaFree(p->d_q); cudaFree(p->d_plane2); cudaFree(p->d_plane);
+  cudaFree(p->d_kvlast); cudaFree(p->d_elem); cudaFree(p->d_shell_off); cudaFree(p->d_tickets);
+  cudaFree(p->d_spec);
+  for (int i = 0; i < 2; ++i) {
+    cudaFree(p->d_stage[i]); cudaFree(p->d_out[i]); cudaFree(p->d_pidx[i]); cudaFree(p->d_npk[i]);
+    if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
+    if (p->ev_done[i]) cudaEventDestroy(p->ev_done[i]);
+    if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
+  }
+  if (p->s_copy) cudaStreamDestroy(p->s_copy);
+  if (p->s_comp) cudaStreamDestroy(p->s_comp);
+  delete p;
+}
+
+static const size_t kMaxDynSmem = 200 * 1024;
+
+extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, int ndim, const int64_t* N,
+                                          const double* L, int cutoff, double threshold, int max_batch,
+                                          int path) {
+  if (!out || !N || !L) return fail(SBX_EINVAL, "NULL argument");
+  *out = nullptr;
+  if (max_batch < 1) return fail(SBX_EINVAL, "max_batch must be >= 1");
+  int rc;
+  if (device == SBX_DEVICE_NONE) {
+    // geometry-only plan: shell table on the host, no CUDA call; *_execute refuses to run
+    sbx_scatter_plan* hp = new (std::nothrow) sbx_scatter_plan();
+    if (!hp) return fail(SBX_ENOMEM, "out of host memory");
+    hp->device = SBX_DEVICE_NONE;
+    if ((rc = build_shell_table(hp->tab, ndim, N, L, cutoff, threshold))) { delete hp; return rc; }
+    fill_q(hp);
+    hp->path = SBX_SCATTER_AUTO;
+    *out = hp;
+    return SBX_OK;
+  }
+  if ((rc = require_sm100(device))) return rc;
+  DeviceGuard guard(device);
+  sbx_scatter_plan* p = new (std::nothrow) sbx_scatter_plan();
+  if (!p) return fail(SBX_ENOMEM, "out of host memory");
+  p->device = device;
+  p->max_batch = max_batch;
+  if ((rc = build_shell_table(p->tab, ndim, N, L, cutoff, threshold))) { free_plan(p); return rc; }
+  fill_q(p);
+  if ((rc = build_device_tables(p))) { free_plan(p); return rc; }
+  cudaDeviceGetAttribute(&p->sm_count, cudaDevAttrMultiProcessorCount, device);
+
+  const GridDev& g = p->grid;
+  if (path == SBX_SCATTER_AUTO)
+    path = (p->tab.n_members() * 4 <= g.nspec) ? SBX_SCATTER_FFT_GATHER : SBX_SCATTER_FFT_DENSE;
+  if (path != SBX_SCATTER_FFT_DENSE && path != SBX_SCATTER_FFT_GATHER) {
+    free_plan(p);
+    return fail(SBX_EINVAL, "scatter path %d is not available in this build", path);
+  }
+  p->path = path;
+  if ((size_t)p->tab.n_shells() * 3 * sizeof(double) > kMaxDynSmem) {
+    free_plan(p);
+    return fail(SBX_EINVAL, "%d shells exceed the shared-memory shell table (max %zu)", p->tab.n_shells(),
+                kMaxDynSmem / 24);
+  }
+
+  // fields per cuFFT launch: keep field + spectrum of one chunk inside the 126 MB L2
+  const size_t per_field = (size_t)g.nreal * 8 + (size_t)g.nspec * 16;
+  size_t chunk = (size_t)64 << 20;
+  chunk = std::max<size_t>(1, chunk / per_field);
+  if (const char* e = getenv("SBX_FFT_CHUNK")) chunk = std::max(1, atoi(e));
+  p->chunk = (int)std::min<size_t>(chunk, (size_t)max_batch);
+  const long long want = (4LL * p->sm_count + p->chunk - 1) / p->chunk;
+  long long bpf = std::max<long long>((g.nspec + 16383) / 16384, want);
+  bpf = std::min<long long>(bpf, std::max<long long>(1, g.nspec / 256));
+  p->blocks_per_field = (int)std::min<long long>(bpf, 65535);
+
+  cudaError_t e = cudaMalloc((void**)&p->d_spec, (size_t)p->chunk * g.nspec * sizeof(double2));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_tickets, (size_t)max_batch * sizeof(unsigned));
+  if (e == cudaSuccess) e = cudaMemset(p->d_tickets, 0, (size_t)max_batch * sizeof(unsigned));
+  if (e != cudaSuccess) {
+    free_plan(p);
+    return fail(e == cudaErrorMemoryAllocation ? SBX_ENOMEM : SBX_ECUDA, "plan allocation: %s", cudaGetErrorString(e));
+  }
+  cufftHandle h;
+  if ((rc = get_fft(p, p->chunk, &h))) { free_plan(p); return rc; }
+  cudaFuncSetAttribute(shell_histogram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(shell_histogram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(shell_histogram_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(shell_gather_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(peaks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  *out = p;
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_plan_create(sbx_scatter_plan** out, int device, int ndim, const int64_t* N,
+                                       const double* L, int cutoff, double threshold, int max_batch) {
+  return sbx_scatter_plan_create_ex(out, device, ndim, N, L, cutoff, threshold, max_batch, SBX_SCATTER_AUTO);
+}
+
+extern "C" int sbx_scatter_plan_destroy(sbx_scatter_plan* plan) {
+  free_plan(plan);
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_plan_path(const sbx_scatter_plan* plan) { return plan ? plan->path : SBX_EINVAL; }
+
+extern "C" int sbx_scatter_plan_shells(const sbx_scatter_plan* plan, int* n_shells, double* q_host,
+                                       int64_t* count_host) {
+  if (!plan || !n_shells) return fail(SBX_EINVAL, "NULL argument");
+  *n_shells = plan->tab.n_shells();
+  for (int s = 0; s < *n_shells; ++s) {
+    if (q_host) q_host[s] = plan->q_host[s];
+    if (count_host) count_host[s] = plan->tab.count[s];
+  }
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_plan_members(const sbx_scatter_plan* plan, int shell, int64_t* n, double* k2xyz_host,
+                                        int64_t capacity) {
+  if (!plan || !n) return fail(SBX_EINVAL, "NULL argument");
+  const ShellTable& t = plan->tab;
+  if (shell < 0 || shell >= t.n_shells()) return fail(SBX_EINVAL, "shell %d out of range", shell);
+  const auto& mem = t.members[shell];
+  *n = (int64_t)mem.size();
+  if (!k2xyz_host) return SBX_OK;
+  if (capacity < *n) return fail(SBX_ERANGE, "member buffer holds %lld, need %lld", (long long)capacity, (long long)*n);
+  for (size_t j = 0; j < mem.size(); ++j) {  // txyz row of scatter.py:82: (kv0[a], kv1[b], kv2[c])
+    int64_t r = mem[j];
+    for (int d = t.ndim - 1; d >= 0; --d) {
+      k2xyz_host[j * t.ndim + d] = t.kv[d][r % t.N[d]];
+      r /= t.N[d];
+    }
+  }
+  return SBX_OK;
+}
+
+// ------------------------------------------------------------------------------ execution
+static int check_peaks_args(int n, int step, int max_peaks) {
+  if (step < 1 || step > 16384) return fail(SBX_EINVAL, "step must be in 1..16384, got %d", step);
+  if (max_peaks < 0) return fail(SBX_EINVAL, "max_peaks must be >= 0");
+  if ((peaks_smem_doubles(n, step) + (size_t)n) * sizeof(double) > kMaxDynSmem)
+    return fail(SBX_EINVAL, "n=%d rows with step=%d exceed the peak-search shared memory", n, step);
+  return SBX_OK;
+}
+
+// scatter (+ optional fused peaks) on `batch` device-resident fields
+static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, double* shell_I, bool do_peaks,
+                       const PeakParams& pp, double* plot_y, int32_t* peak_idx, int32_t* n_peaks,
+                       cudaStream_t st) {
+  if (!p || !fields || !shell_I) return fail(SBX_EINVAL, "NULL argument");
+  if (p->device == SBX_DEVICE_NONE) return fail(SBX_ENODEVICE, "geometry-only plan: no device to execute on");
+  if (batch < 1 || batch > p->max_batch) return fail(SBX_EINVAL, "batch %d outside 1..max_batch=%d", batch, p->max_batch);
+  DeviceGuard guard(p->device);
+  const GridDev& g = p->grid;
+  const ShellDev& sh = p->shell;
+  const int ns = sh.n_shells;
+  int rc;
+  if (do_peaks && (rc = check_peaks_args(ns, pp.step, pp.max_peaks))) return rc;
+  const size_t smem_peaks = do_peaks ? (peaks_smem_doubles(ns, pp.step) + ns) * sizeof(double) : 0;
+  for (int c0 = 0; c0 < batch; c0 += p->chunk) {
+    const int nb = std::min(p->chunk, batch - c0);
+    cufftHandle h;
+    if ((rc = get_fft(p, nb, &h))) return rc;
+    SBX_CUFFT(cufftSetStream(h, st));
+    SBX_CUFFT(cufftExecD2Z(h, const_cast<double*>(fields) + (size_t)c0 * g.nreal, (cufftDoubleComplex*)p->d_spec));
+    double* outI = shell_I + (size_t)c0 * ns;
+    double* py = plot_y ? plot_y + (size_t)c0 * pp.step : nullptr;
+    int32_t* pi = peak_idx ? peak_idx + (size_t)c0 * pp.max_peaks : nullptr;
+    int32_t* np_ = n_peaks ? n_peaks + c0 : nullptr;
+    if (p->path == SBX_SCATTER_FFT_GATHER) {
+      const size_t smem = std::max(smem_peaks, (size_t)ns * sizeof(double));
+      shell_gather_kernel<<<nb, 256, smem, st>>>(p->d_spec, g.nspec, g.factor, p->d_elem, p->d_shell_off, ns, outI,
+                                                 do_peaks ? 1 : 0, p->d_q, pp, py, pi, np_);
+    } else {
+      SBX_CUDA(cudaMemsetAsync(outI, 0, (size_t)nb * ns * sizeof(double), st));
+      const size_t smem = std::max(smem_peaks, (size_t)2 * ns * sizeof(double));
+      dim3 grid(p->blocks_per_field, nb);
+      unsigned* tk = do_peaks ? p->d_tickets : nullptr;
+      if (g.ndim == 3)
+        shell_histogram_kernel<3><<<grid, 256, smem, st>>>(p->d_spec, g, sh, outI, tk, do_peaks, p->d_q, pp, py, pi, np_);
+      else if (g.ndim == 2)
+        shell_histogram_kernel<2><<<grid, 256, smem, st>>>(p->d_spec, g, sh, outI, tk, do_peaks, p->d_q, pp, py, pi, np_);
+      else
+        shell_histogram_kernel<1><<<grid, 256, smem, st>>>(p->d_spec, g, sh, outI, tk, do_peaks, p->d_q, pp, py, pi, np_);
+    }
+    SBX_CUDA(cudaGetLastError());
+  }
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_execute(sbx_scatter_plan* plan, const double* fields, int batch, double* shell_I,
+                                   void* stream) {
+  PeakParams pp{};
+  return run_scatter(plan, fields, batch, shell_I, false, pp, nullptr, nullptr, nullptr, (cudaStream_t)stream);
+}
+
+extern "C" int sbx_scatter_peaks_execute(sbx_scatter_plan* plan, const double* fields, int batch, double* shell_I,
+                                         double width, int step, double q_cutoff, double min_height,
+                                         double* plot_y, int32_t* peak_idx, int32_t* n_peaks, int max_peaks,
+                                         void* stream) {
+  PeakParams pp{width, q_cutoff, min_height, step, max_peaks};
+  return run_scatter(plan, fields, batch, shell_I, true, pp, plot_y, peak_idx, n_peaks, (cudaStream_t)stream);
+}
+
+extern "C" int sbx_peaks_execute(const double* q, const double* I, int n, int batch, double width, int step,
+                                 double q_cutoff, double min_height, double* plot_y, int32_t* peak_idx,
+                                 int32_t* n_peaks, int max_peaks, void* stream) {
+  if (!q || !I) return fail(SBX_EINVAL, "NULL argument");
+  if (n < 1 || batch < 1) return fail(SBX_EINVAL, "n and batch must be >= 1");
+  int rc = check_peaks_args(n, step, max_peaks);
+  if (rc) return rc;
+  static thread_local bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(peaks_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+    attr_set = true;
+  }
+  PeakParams pp{width, q_cutoff, min_height, step, max_peaks};
+  const size_t smem = peaks_smem_doubles(n, step) * sizeof(double);
+  peaks_kernel<<<batch, 256, smem, (cudaStream_t)stream>>>(q, I, n, pp, plot_y, peak_idx, n_peaks);
+  SBX_CUDA(cudaGetLastError());
+  return SBX_OK;
+}
+
+// host-buffer streaming: H2D of chunk i+1 overlaps the transform + binning of chunk i
+static int ensure_stage(sbx_scatter_plan* p, int max_peaks) {
+  const GridDev& g = p->grid;
+  if (!p->s_copy) {
+    SBX_CUDA(cudaStreamCreateWithFlags(&p->s_copy, cudaStreamNonBlocking));
+    SBX_CUDA(cudaStreamCreateWithFlags(&p->s_comp, cudaStreamNonBlocking));
+    for (int i = 0; i < 2; ++i) {
+      SBX_CUDA(cudaMalloc((void**)&p->d_stage[i], (size_t)p->max_batch * g.nreal * sizeof(double)));
+      SBX_CUDA(cudaMalloc((void**)&p->d_out[i], (size_t)p->max_batch * p->shell.n_shells * sizeof(double)));
+      SBX_CUDA(cudaMalloc((void**)&p->d_npk[i], (size_t)p->max_batch * sizeof(int32_t)));
+      SBX_CUDA(cudaEventCreateWithFlags(&p->ev_in[i], cudaEventDisableTiming));
+      SBX_CUDA(cudaEventCreateWithFlags(&p->ev_done[i], cudaEventDisableTiming));
+      SBX_CUDA(cudaEventCreateWithFlags(&p->ev_out[i], cudaEventDisableTiming));
+    }
+  }
+  if (max_peaks > p->stage_max_peaks) {
+    for (int i = 0; i < 2; ++i) {
+      cudaFree(p->d_pidx[i]);
+      SBX_CUDA(cudaMalloc((void**)&p->d_pidx[i], (size_t)p->max_batch * max_peaks * sizeof(int32_t)));
+    }
+    p->stage_max_peaks = max_peaks;
+  }
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_execute_host(sbx_scatter_plan* plan, const double* fields_host, int64_t total,
+                                        double* shell_I_host, double width, int step, double q_cutoff,
+                                        double min_height, int32_t* peak_idx_host, int32_t* n_peaks_host,
+                                        int max_peaks) {
+  sbx_scatter_plan* p = plan;
+  if (!p || !fields_host || !shell_I_host) return fail(SBX_EINVAL, "NULL argument");
+  if (p->device == SBX_DEVICE_NONE) return fail(SBX_ENODEVICE, "geometry-only plan: no device to execute on");
+  if (total < 1) return fail(SBX_EINVAL, "total must be >= 1");
+  const bool do_peaks = n_peaks_host != nullptr;
+  if (do_peaks && !peak_idx_host) max_peaks = 0;
+  DeviceGuard guard(p->device);
+  int rc = ensure_stage(p, do_peaks ? std::max(max_peaks, 1) : 0);
+  if (rc) return rc;
+  const GridDev& g = p->grid;
+  const int ns = p->shell.n_shells;
+  PeakParams pp{width, q_cutoff, min_height, step, max_peaks};
+  int64_t done = 0;
+  for (int64_t i = 0; done < total; ++i) {
+    const int slot = (int)(i & 1);
+    const int nb = (int)std::min<int64_t>(p->max_batch, total - done);
+    // the stage buffer is free once the compute that read it (two chunks ago) has finished,
+    // the output buffers once their D2H (two chunks ago) has been issued and completed
+    SBX_CUDA(cudaStreamWaitEvent(p->s_copy, p->ev_done[slot], 0));
+    SBX_CUDA(cudaMemcpyAsync(p->d_stage[slot], fields_host + (size_t)done * g.nreal,
+                             (size_t)nb * g.nreal * sizeof(double), cudaMemcpyHostToDevice, p->s_copy));
+    SBX_CUDA(cudaEventRecord(p->ev_in[slot], p->s_copy));
+    SBX_CUDA(cudaStreamWaitEvent(p->s_comp, p->ev_in[slot], 0));
+    SBX_CUDA(cudaStreamWaitEvent(p->s_comp, p->ev_out[slot], 0));
+    rc = run_scatter(p, p->d_stage[slot], nb, p->d_out[slot], do_peaks, pp, nullptr,
+                     do_peaks && max_peaks ? p->d_pidx[slot] : nullptr, do_peaks ? p->d_npk[slot] : nullptr,
+                     p->s_comp);
+    if (rc) return rc;
+    // results ride the compute stream so that they never queue behind the next big H2D
+    SBX_CUDA(cudaMemcpyAsync(shell_I_host + (size_t)done * ns, p->d_out[slot], (size_t)nb * ns * sizeof(double),
+                             cudaMemcpyDeviceToHost, p->s_comp));
+    if (do_peaks) {
+      SBX_CUDA(cudaMemcpyAsync(n_peaks_host + done, p->d_npk[slot], (size_t)nb * sizeof(int32_t),
+                               cudaMemcpyDeviceToHost, p->s_comp));
+      if (max_peaks)
+        SBX_CUDA(cudaMemcpyAsync(peak_idx_host + (size_t)done * max_peaks, p->d_pidx[slot],
+                                 (size_t)nb * max_peaks * sizeof(int32_t), cudaMemcpyDeviceToHost, p->s_comp));
+    }
+    SBX_CUDA(cudaEventRecord(p->ev_done[slot], p->s_comp));
+    SBX_CUDA(cudaEventRecord(p->ev_out[slot], p->s_comp));
+    done += nb;
+  }
+  SBX_CUDA(cudaStreamSynchronize(p->s_comp));
+  SBX_CUDA(cudaStreamSynchronize(p->s_copy));
+  return SBX_OK;
+}

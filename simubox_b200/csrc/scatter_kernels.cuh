@@ -1,0 +1,213 @@
+// scatter_kernels.cuh -- fused |F|^2 / |q|-shell kernels (sm_100a).
+//
+// Replaces the hstack + argsort + merge loop of Scatter.sacttering_peak
+// (SimuBox/calculator/scatter.py:86-118).  The spectrum is the cuFFT D2Z half spectrum
+// (last axis stored 0..N/2); every stored element is binned for itself and, when it has one,
+// for its Hermitian mirror, each with the k^2 the reference pairs with that full-spectrum
+// position (quirk Q1).  All k^2 arithmetic is two table look-ups and
+// two adds, performed with __dadd_rn so that host table and device agree bit for bit.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "peaks.cuh"
+
+namespace sbx {
+
+struct ShellDev {
+  const double* rep;  // n_shells ascending k^2 of each shell's first member
+  int n_shells;
+  int truncated;       // last shell keeps only `designated`
+  long long designated;
+  double threshold;
+  double vcut;  // conservative upper bound: k^2 > vcut can never be binned
+};
+
+struct GridDev {
+  int ndim;
+  int N0, N1, N2;      // unused trailing dims = 1
+  int H;               // stored length of the last axis = N_last/2 + 1
+  long long nspec;     // stored elements per field
+  long long nreal;     // real samples per field
+  const double2* plane2;  // 3D: per (a,b) row {plane k^2 of F[a,b,.], plane k^2 of its mirror row}
+  const double* plane;    // 1D/2D: k^2 per full-spectrum position (N0 or N0*N1 entries)
+  const double* kvlast;   // 3D: kv2[c], c < H
+  double factor;          // 1 / prod(N)  (scatter.py:84)
+};
+
+// largest s with rep[s] <= v (v >= rep[0] = smallest k^2 of the grid)
+__device__ __forceinline__ int shell_search(const double* rep, int n, double v) {
+  int lo = 0, hi = n;  // invariant: rep[lo] <= v < rep[hi]
+  while (hi - lo > 1) {
+    const int mid = (lo + hi) >> 1;
+    if (rep[mid] <= v) lo = mid; else hi = mid;
+  }
+  return lo;
+}
+
+// shell id for k^2 value v at full-spectrum index f, or -1 if the reference would not bin it
+__device__ __forceinline__ int shell_of(const ShellDev& sh, const double* rep_s, double v, long long f) {
+  const int s = shell_search(rep_s, sh.n_shells, v);
+  if (fabs(__dsub_rn(rep_s[s], v)) > sh.threshold) return -1;  // beyond the table (scatter.py:108)
+  if (sh.truncated && s == sh.n_shells - 1 && f != sh.designated) return -1;  // scatter.py:106-107
+  return s;
+}
+
+__device__ __forceinline__ double intensity(const double2 z, double factor) {
+  // factor * |F^2| (scatter.py:92); |F^2| = re^2 + im^2 up to 1 ulp
+  return factor * (z.x * z.x + z.y * z.y);
+}
+
+// ------------------------------------------------------------------------------------------
+// Dense path: full scan of the stored spectrum, shared-memory shell histogram per block,
+// one global RED per touched bin per block.  grid = (blocks_per_field, batch).
+// The last block to finish a field optionally runs the peak search on the finished row.
+// ------------------------------------------------------------------------------------------
+template <int NDIM>
+__global__ void __launch_bounds__(256)
+shell_histogram_kernel(const double2* __restrict__ spec, GridDev g, ShellDev sh,
+                       double* __restrict__ shell_I, unsigned int* __restrict__ tickets,
+                       int do_peaks, const double* __restrict__ q, PeakParams pp,
+                       double* __restrict__ plot_y, int32_t* __restrict__ peak_idx,
+                       int32_t* __restrict__ n_peaks) {
+  extern __shared__ double smem[];
+  double* rep_s = smem;                 // n_shells
+  double* bins = smem + sh.n_shells;    // n_shells
+  const int field = blockIdx.y;
+  const int tid = threadIdx.x;
+  for (int s = tid; s < sh.n_shells; s += blockDim.x) {
+    rep_s[s] = sh.rep[s];
+    bins[s] = 0.0;
+  }
+  __syncthreads();
+
+  const double2* fs = spec + (long long)field * g.nspec;
+  const long long per_block = (g.nspec + gridDim.x - 1) / gridDim.x;
+  const long long e0 = (long long)blockIdx.x * per_block;
+  const long long e1 = min(e0 + per_block, g.nspec);
+  const int halfLast = g.H - 1;  // N_last / 2
+  bool any = false;
+
+  for (long long e = e0 + tid; e < e1; e += blockDim.x) {
+    double v1, v2;
+    long long f1, f2;
+    bool has_mirror;
+    if (NDIM == 3) {
+      const long long row = e / g.H;
+      const int c = (int)(e - row * g.H);
+      const double2 p2 = g.plane2[row];
+      if (fmin(p2.x, p2.y) > sh.vcut) continue;  // whole row beyond the table: never loaded
+      const double kc = g.kvlast[c];
+      v1 = __dadd_rn(p2.x, kc);
+      v2 = __dadd_rn(p2.y, kc);
+      has_mirror = (c != 0) && (c != halfLast);
+      f1 = row * g.N2 + c;
+      f2 = -1;
+      if (has_mirror && sh.truncated) {  // only needed for the designated-member test
+        const int a = (int)(row / g.N1), b = (int)(row - (long long)a * g.N1);
+        const long long mrow = (long long)(a ? g.N0 - a : 0) * g.N1 + (b ? g.N1 - b : 0);
+        f2 = mrow * g.N2 + (g.N2 - c);
+      }
+    } else if (NDIM == 2) {
+      const int a = (int)(e / g.H), b = (int)(e - (long long)a * g.H);
+      f1 = (long long)a * g.N1 + b;
+      has_mirror = (b != 0) && (b != halfLast);
+      f2 = (long long)(a ? g.N0 - a : 0) * g.N1 + (g.N1 - b);
+      v1 = g.plane[f1];
+      v2 = has_mirror ? g.plane[f2] : 0.0;
+    } else {
+      f1 = e;
+      has_mirror = (e != 0) && (e != halfLast);
+      f2 = g.N0 - e;
+      v1 = g.plane[f1];
+      v2 = has_mirror ? g.plane[f2] : 0.0;
+    }
+    const bool h1 = v1 <= sh.vcut;
+    const bool h2 = has_mirror && v2 <= sh.vcut;
+    if (!(h1 || h2)) continue;
+    const double inten = intensity(fs[e], g.factor);
+    if (h1) {
+      const int s = shell_of(sh, rep_s, v1, f1);
+      if (s >= 0) { atomicAdd(&bins[s], inten); any = true; }
+    }
+    if (h2) {
+      const int s = shell_of(sh, rep_s, v2, f2);
+      if (s >= 0) { atomicAdd(&bins[s], inten); any = true; }
+    }
+  }
+  const int block_any = __syncthreads_or(any ? 1 : 0);
+  if (block_any) {
+    double* out = shell_I + (long long)field * sh.n_shells;
+    for (int s = tid; s < sh.n_shells; s += blockDim.x) {
+      const double v = bins[s];
+      if (v != 0.0) atomicAdd(&out[s], v);
+    }
+  }
+  if (!tickets) return;
+
+  // last-arriving block of this field: peak search on the finished shell row
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (tid == 0) {
+    const unsigned t = atomicAdd(&tickets[field], 1u);
+    s_last = (t == gridDim.x - 1);
+    if (s_last) tickets[field] = 0;  // re-arm for the next launch
+  }
+  __syncthreads();
+  if (!s_last || !do_peaks) return;
+  __threadfence();
+  double* row = smem;  // reuse: n_shells doubles for I, then the peaks scratch
+  for (int s = tid; s < sh.n_shells; s += blockDim.x)
+    row[s] = __ldcg(shell_I + (long long)field * sh.n_shells + s);
+  __syncthreads();
+  peaks_block(q, row, sh.n_shells, pp, plot_y ? plot_y + (long long)field * pp.step : nullptr,
+              peak_idx ? peak_idx + (long long)field * pp.max_peaks : nullptr,
+              n_peaks ? n_peaks + field : nullptr, smem + sh.n_shells);
+}
+
+// ------------------------------------------------------------------------------------------
+// Gather path: the shell members are known on the host (field independent), so only those
+// spectrum elements are read.  One block per field, one warp per shell at a time; every lane
+// sums its members in list order and the warp combines with a fixed shuffle tree, so the
+// result is bitwise reproducible.  The same block then runs the peak search.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+shell_gather_kernel(const double2* __restrict__ spec, long long nspec, double factor,
+                    const long long* __restrict__ elem, const int* __restrict__ shell_off,
+                    int n_shells, double* __restrict__ shell_I, int do_peaks,
+                    const double* __restrict__ q, PeakParams pp, double* __restrict__ plot_y,
+                    int32_t* __restrict__ peak_idx, int32_t* __restrict__ n_peaks) {
+  extern __shared__ double smem[];
+  const int field = blockIdx.x;
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5, nwarp = blockDim.x >> 5;
+  const double2* fs = spec + (long long)field * nspec;
+  for (int s = warp; s < n_shells; s += nwarp) {
+    double acc = 0.0;
+    for (int m = shell_off[s] + lane; m < shell_off[s + 1]; m += 32) acc += intensity(__ldg(&fs[elem[m]]), factor);
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+      smem[s] = acc;
+      shell_I[(long long)field * n_shells + s] = acc;
+    }
+  }
+  if (!do_peaks) return;
+  __syncthreads();
+  peaks_block(q, smem, n_shells, pp, plot_y ? plot_y + (long long)field * pp.step : nullptr,
+              peak_idx ? peak_idx + (long long)field * pp.max_peaks : nullptr,
+              n_peaks ? n_peaks + field : nullptr, smem + n_shells);
+}
+
+// stand-alone peak search (sbx_peaks_execute): one block per field
+__global__ void __launch_bounds__(256)
+peaks_kernel(const double* __restrict__ q, const double* __restrict__ I, int n, PeakParams pp,
+             double* __restrict__ plot_y, int32_t* __restrict__ peak_idx, int32_t* __restrict__ n_peaks) {
+  extern __shared__ double smem[];
+  const int field = blockIdx.x;
+  peaks_block(q, I + (long long)field * n, n, pp, plot_y ? plot_y + (long long)field * pp.step : nullptr,
+              peak_idx ? peak_idx + (long long)field * pp.max_peaks : nullptr,
+              n_peaks ? n_peaks + field : nullptr, smem);
+}
+
+}  // namespace sbx

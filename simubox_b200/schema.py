@@ -1,0 +1,129 @@
+"""Data models of the density-analysis path, field-for-field compatible with the reference.
+
+Mirrors ``SimuBox/schema/structs/DataFile.py:77-172`` (``Density``, ``DensityParseResult``,
+``Printout``), ``ComputedRes.py:31-48`` (``ScatterResult``, ``ScatterPlot``, ``OpenCVResult``),
+``MixinStructs.py`` and the enums of ``schema/enums/Modes.py:13-71`` that the entry points
+accept.  ``fig`` / ``ax`` are typed ``Any`` because matplotlib is optional here (no graphics
+stack on the GPU box); they are ``None`` unless matplotlib is importable and a plot is asked for.
+"""
+from __future__ import annotations
+
+from enum import Enum
+from pathlib import Path
+from typing import Any, Optional, Sequence, Union
+
+import numpy as np
+import pandas as pd
+from pydantic import BaseModel, ConfigDict
+
+RealNum = Union[int, float]
+PathLike = Union[Path, str]
+FileLike = Union[Path, str, bytes]
+
+
+class StrEnum(str, Enum):
+    def __str__(self) -> str:  # reference enums print as their value
+        return str(self.value)
+
+
+class ColorMode(StrEnum):
+    RGB = "rgb"
+    HEX = "hex"
+    L = "l"
+    RANDOM = "random"
+
+
+class AnalyzeMode(StrEnum):
+    VORONOI = "voronoi"
+    TRIANGLE = "triangle"
+    WEIGHTED = "weighted"
+
+
+class WeightedMode(StrEnum):
+    ADDITIVE = "additive"
+    POWER = "power"
+
+
+class MixinBaseModel(BaseModel):
+    model_config = ConfigDict(arbitrary_types_allowed=True)
+
+
+class FigureAxesMixin(MixinBaseModel):
+    fig: Optional[Any] = None
+    ax: Optional[Any] = None
+
+
+class Printout(MixinBaseModel):
+    """Subset of the reference ``Printout`` that the density path reads (DataFile.py:17-33)."""
+    path: Path
+    box: np.ndarray
+    lxlylz: np.ndarray
+    step: int
+    freeEnergy: float
+    freeU: float
+    freeW: float
+    freeS: float
+    freeWS: float
+    inCompMax: float
+    volumes: Optional[np.ndarray] = None
+    potentials: Optional[np.ndarray] = None
+
+
+class Density(MixinBaseModel):
+    """Parsed phout/phin/block file (reference DataFile.py:77-86)."""
+    path: Optional[Path] = None
+    data: pd.DataFrame
+    NxNyNz: Optional[np.ndarray] = None
+    lxlylz: Optional[np.ndarray] = None
+    shape: Optional[np.ndarray] = None
+
+    def _axis_mask(self):
+        return None if self.NxNyNz is None else (np.asarray(self.NxNyNz) != 1)
+
+    def _repair_box(self, box: np.ndarray):
+        # DataFile.py:88-115: only fill the box when the file gave none (all ones).
+        keep = self._axis_mask()
+        if self.lxlylz is None or (all(self.lxlylz == 1) and any(box != 1)):
+            self.lxlylz = box if keep is None else box[keep]
+
+    def repair_from_printout(self, printout: Printout):
+        self._repair_box(np.asarray(printout.lxlylz))
+
+    def repair_from_fet(self, fet):
+        self._repair_box(np.array([fet.lx, fet.ly, fet.lz]))
+
+
+class DensityParseResult(MixinBaseModel):
+    """Reference DataFile.py:159-172."""
+    path: Optional[Path] = None
+    raw_NxNyNz: np.ndarray
+    raw_lxlylz: np.ndarray
+    raw_mat: np.ndarray
+    lxlylz: np.ndarray
+    NxNyNz: np.ndarray
+    mat: np.ndarray
+    expand: np.ndarray
+    target: list[int]
+
+
+class ScatterResult(MixinBaseModel):
+    """Reference ComputedRes.py:31-34."""
+    parsed_density: DensityParseResult
+    q_Intensity: np.ndarray
+    q_idx: dict
+
+
+class ScatterPlot(FigureAxesMixin):
+    """Reference ComputedRes.py:37-41."""
+    peaks_location: np.ndarray
+    peaks_height: dict
+    plot_y: np.ndarray
+    plot_x: np.ndarray
+
+
+class OpenCVResult(MixinBaseModel):
+    """Reference ComputedRes.py:44-48."""
+    path: Optional[Path]
+    parsed_density: DensityParseResult
+    facets: Sequence
+    centers: np.ndarray
