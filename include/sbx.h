@@ -83,6 +83,14 @@ int sbx_scatter_plan_members(const sbx_scatter_plan* plan, int shell, int64_t* n
 /* which SBX_SCATTER_* path the plan runs */
 int sbx_scatter_plan_path(const sbx_scatter_plan* plan);
 
+/* Live profiling for bench.py: when enabled every chunk launch is bracketed by CUDA events on
+ * the launching stream.  get_profile synchronises on the last event and returns the summed
+ * device time of the transform stage and of the hand-written fused kernel, the number of this
+ * library's own kernel launches and of transform calls since the last reset. */
+int sbx_scatter_plan_set_profiling(sbx_scatter_plan* plan, int enable);
+int sbx_scatter_plan_get_profile(sbx_scatter_plan* plan, double* transform_ms, double* fused_ms,
+                                 int64_t* own_launches, int64_t* transform_calls, int reset);
+
 /* fields: batch x prod(N) fp64, C order (= DensityParseResult.mat of each field);
  * shell_I: batch x n_shells fp64 = q_Intensity[:,1] per field.  batch <= max_batch. */
 int sbx_scatter_execute(sbx_scatter_plan* plan, const double* fields, int batch, double* shell_I,

@@ -33,6 +33,8 @@ _SIGNATURES = {
     "sbx_scatter_plan_shells": (C.c_int, [_vp, C.POINTER(C.c_int), _f64p, _i64p]),
     "sbx_scatter_plan_members": (C.c_int, [_vp, C.c_int, _i64p, _f64p, C.c_int64]),
     "sbx_scatter_plan_path": (C.c_int, [_vp]),
+    "sbx_scatter_plan_set_profiling": (C.c_int, [_vp, C.c_int]),
+    "sbx_scatter_plan_get_profile": (C.c_int, [_vp, _f64p, _f64p, _i64p, _i64p, C.c_int]),
     "sbx_scatter_execute": (C.c_int, [_vp, _vp, C.c_int, _vp, _vp]),
     "sbx_peaks_execute": (C.c_int, [_vp, _vp, C.c_int, C.c_int, C.c_double, C.c_int, C.c_double, C.c_double, _vp, _vp, _vp, C.c_int, _vp]),
     "sbx_scatter_peaks_execute": (C.c_int, [_vp, _vp, C.c_int, _vp, C.c_double, C.c_int, C.c_double, C.c_double, _vp, _vp, _vp, C.c_int, _vp]),
@@ -120,6 +122,15 @@ class ScatterPlan:
 
     def q_idx(self) -> dict:
         return {s: list(self.members(s)) for s in range(self.n_shells)}
+
+    def set_profiling(self, enable: bool):
+        check(lib().sbx_scatter_plan_set_profiling(self._h, int(enable)))
+
+    def profile(self, reset: bool = True) -> dict:
+        a, b = C.c_double(), C.c_double()
+        n, m = C.c_int64(), C.c_int64()
+        check(lib().sbx_scatter_plan_get_profile(self._h, C.byref(a), C.byref(b), C.byref(n), C.byref(m), int(reset)))
+        return dict(transform_ms=a.value, fused_ms=b.value, own_launches=n.value, transform_calls=m.value)
 
     def close(self):
         if self._h:

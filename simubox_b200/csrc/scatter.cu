@@ -81,7 +81,23 @@ struct sbx_scatter_plan {
   int32_t* d_npk[2] = {nullptr, nullptr};
   int stage_max_peaks = 0;
   cudaEvent_t ev_in[2] = {nullptr, nullptr}, ev_done[2] = {nullptr, nullptr}, ev_out[2] = {nullptr, nullptr};
+  // live profiling (sbx_scatter_plan_set_profiling): event triples around transform / fused kernel
+  bool profiling = false;
+  std::vector<cudaEvent_t> prof_events;  // 3 per chunk launch: start, after transform, after fused kernel
+  size_t prof_used = 0;
+  long long own_launches = 0, fft_calls = 0;
 };
+
+static cudaEvent_t prof_event(sbx_scatter_plan* p, cudaStream_t st) {
+  if (p->prof_used == p->prof_events.size()) {
+    cudaEvent_t e;
+    cudaEventCreate(&e);
+    p->prof_events.push_back(e);
+  }
+  cudaEvent_t e = p->prof_events[p->prof_used++];
+  cudaEventRecord(e, st);
+  return e;
+}
 
 static int get_fft(sbx_scatter_plan* p, int batch, cufftHandle* out) {
   auto it = p->fft.find(batch);
@@ -186,6 +202,7 @@ static void free_plan(sbx_scatter_plan* p) {
   if (p->device == SBX_DEVICE_NONE) { delete p; return; }
   DeviceGuard guard(p->device);
   for (auto& kv : p->fft) cufftDestroy(kv.second);
+  for (cudaEvent_t e : p->prof_events) cudaEventDestroy(e);
   cudaFree(p->d_rep); cudaFree(p->d_q); cudaFree(p->d_plane2); cudaFree(p->d_plane);
   cudaFree(p->d_kvlast); cudaFree(p->d_elem); cudaFree(p->d_shell_off); cudaFree(p->d_tickets);
   cudaFree(p->d_spec);
@@ -344,7 +361,11 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
     cufftHandle h;
     if ((rc = get_fft(p, nb, &h))) return rc;
     SBX_CUFFT(cufftSetStream(h, st));
+    if (p->profiling) prof_event(p, st);
     SBX_CUFFT(cufftExecD2Z(h, const_cast<double*>(fields) + (size_t)c0 * g.nreal, (cufftDoubleComplex*)p->d_spec));
+    if (p->profiling) prof_event(p, st);
+    p->fft_calls += 1;
+    p->own_launches += 1;
     double* outI = shell_I + (size_t)c0 * ns;
     double* py = plot_y ? plot_y + (size_t)c0 * pp.step : nullptr;
     int32_t* pi = peak_idx ? peak_idx + (size_t)c0 * pp.max_peaks : nullptr;
@@ -366,6 +387,40 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
         shell_histogram_kernel<1><<<grid, 256, smem, st>>>(p->d_spec, g, sh, outI, tk, do_peaks, p->d_q, pp, py, pi, np_);
     }
     SBX_CUDA(cudaGetLastError());
+    if (p->profiling) prof_event(p, st);
+  }
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_plan_set_profiling(sbx_scatter_plan* plan, int enable) {
+  if (!plan) return fail(SBX_EINVAL, "NULL argument");
+  plan->profiling = enable != 0;
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_plan_get_profile(sbx_scatter_plan* plan, double* transform_ms, double* fused_ms,
+                                            int64_t* own_launches, int64_t* transform_calls, int reset) {
+  if (!plan) return fail(SBX_EINVAL, "NULL argument");
+  double a = 0.0, b = 0.0;
+  if (plan->device != SBX_DEVICE_NONE && plan->prof_used) {
+    DeviceGuard guard(plan->device);
+    SBX_CUDA(cudaEventSynchronize(plan->prof_events[plan->prof_used - 1]));
+    for (size_t i = 0; i + 3 <= plan->prof_used; i += 3) {
+      float t0 = 0.f, t1 = 0.f;
+      cudaEventElapsedTime(&t0, plan->prof_events[i], plan->prof_events[i + 1]);
+      cudaEventElapsedTime(&t1, plan->prof_events[i + 1], plan->prof_events[i + 2]);
+      a += t0;
+      b += t1;
+    }
+  }
+  if (transform_ms) *transform_ms = a;
+  if (fused_ms) *fused_ms = b;
+  if (own_launches) *own_launches = plan->own_launches;
+  if (transform_calls) *transform_calls = plan->fft_calls;
+  if (reset) {
+    plan->prof_used = 0;
+    plan->own_launches = 0;
+    plan->fft_calls = 0;
   }
   return SBX_OK;
 }

@@ -1,0 +1,160 @@
+"""GPU parity suite for the scattering path: CUDA (through the C ABI) vs the golden vectors of
+the live reference and vs the numpy oracle on seeded inputs; size-independent properties at
+the BASELINE sizes.  Tolerances: q bit-exact; shell I within
+1e-9*|ref| + 1e-12*max(ref); peak indices exact; plot_y within 1e-9 relative."""
+import json
+
+import numpy as np
+import pytest
+
+from conftest import check_scatter_rows, golden, golden_field, golden_names
+from oracle import scatter_np
+from test_oracle_golden import last_shell_members
+
+pytestmark = pytest.mark.gpu
+
+DENSE, GATHER = 1, 2
+
+
+@pytest.fixture(scope="module")
+def torch_cuda():
+    import torch
+
+    assert torch.cuda.is_available(), "GPU tests need a CUDA device"
+    return torch
+
+
+def run_scatter(sbx_lib, torch, mats, L, cutoff, thr, path, peaks=None):
+    from simubox_b200 import Scatter
+
+    fields = torch.from_numpy(np.ascontiguousarray(np.stack(mats))).cuda()
+    kw = dict(peaks=True, width=peaks["width"], step=peaks["step"], peak_cutoff=peaks["cutoff"],
+              min_height=peaks["min_height"]) if peaks else {}
+    out = Scatter.sacttering_peak_batch(fields, L, cutoff=cutoff, threshold=thr, path=path, max_batch=len(mats), **kw)
+    torch.cuda.synchronize()
+    return out
+
+
+@pytest.mark.parametrize("path", [DENSE, GATHER])
+@pytest.mark.parametrize("name", golden_names("scatter_"))
+def test_scatter_matches_reference_golden(sbx_lib, torch_cuda, name, path):
+    g = golden(name)
+    mat, L, cutoff, thr = golden_field(g), g["L"], int(g["cutoff"]), float(g["threshold"])
+    out = run_scatter(sbx_lib, torch_cuda, [mat], L, cutoff, thr, path)
+    qI = np.stack([out["q"], out["I"][0].cpu().numpy()], axis=1)
+    check_scatter_rows(qI, g["q_Intensity"], cutoff, last_shell_members(mat, L, cutoff, thr))
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names("scatter_") if "peaks_index" in golden(n).files])
+def test_fused_peaks_match_reference_golden(sbx_lib, torch_cuda, name):
+    g = golden(name)
+    kw = json.loads(str(g["peak_kw"]))
+    mat, L, cutoff, thr = golden_field(g), g["L"], int(g["cutoff"]), float(g["threshold"])
+    for path in (DENSE, GATHER):
+        out = run_scatter(sbx_lib, torch_cuda, [mat, mat], L, cutoff, thr, path, peaks=kw)
+        for b in range(2):
+            n = int(out["n_peaks"][b])
+            assert np.array_equal(out["peak_idx"][b, :n].cpu().numpy(), g["peaks_index"]), (path, b)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names("scatter_") if "peaks_index" in golden(n).files])
+def test_show_peak_api_matches_reference_golden(sbx_lib, torch_cuda, name):
+    """Scatter.show_peak (stand-alone peaks kernel) fed the REFERENCE's q_Intensity."""
+    from simubox_b200 import Scatter
+    from simubox_b200.schema import DensityParseResult, ScatterResult
+
+    g = golden(name)
+    kw = json.loads(str(g["peak_kw"]))
+    z = np.zeros(1)
+    parsed = DensityParseResult(raw_NxNyNz=z, raw_lxlylz=z, raw_mat=z, lxlylz=z, NxNyNz=z, mat=z, expand=z, target=[0])
+    sp = Scatter.show_peak(ScatterResult(parsed_density=parsed, q_Intensity=g["q_Intensity"], q_idx={}), **kw)
+    assert np.array_equal(sp.plot_x, g["plot_x"])
+    assert np.allclose(sp.plot_y, g["plot_y"], rtol=1e-9, atol=1e-9 * np.abs(g["plot_y"]).max())
+    assert np.array_equal(sp.peaks_location, g["peaks_location"])
+    assert np.allclose(sp.peaks_height["peak_heights"], g["peak_heights"], rtol=1e-9)
+
+
+def test_drop_in_entry_point_on_density(sbx_lib, torch_cuda):
+    """read_density-style Density -> Scatter.sacttering_peak -> ScatterResult, incl. expand and q_idx."""
+    import pandas as pd
+    from simubox_b200 import Density, Scatter
+
+    g = golden("scatter_phoutC6_t0_unitbox")
+    mat = g["mat"]
+    dens = Density(data=pd.DataFrame(mat.reshape(-1, 1)), NxNyNz=np.array([1, *mat.shape]), lxlylz=g["L"].copy(),
+                   shape=np.array(mat.shape))
+    res = Scatter.sacttering_peak(dens, cutoff=int(g["cutoff"]))
+    check_scatter_rows(res.q_Intensity, g["q_Intensity"], int(g["cutoff"]))
+    counts = np.bincount(g["qidx_shell"], minlength=len(res.q_Intensity))
+    assert [len(res.q_idx[s]) for s in range(len(counts))] == list(counts)
+    res3 = Scatter.sacttering_peak(dens, cutoff=12, expand=3)
+    tiled = np.pad(mat, [(n, n) for n in mat.shape], "wrap")
+    ref, _ = scatter_np.scattering_peak(tiled, g["L"] * 3, 12, 1e-12)
+    check_scatter_rows(res3.q_Intensity, ref, 12)
+
+
+@pytest.mark.parametrize("shape,L,cutoff", [((20, 12, 14), (3.0, 2.0, 2.5), 40), ((24, 24, 24), (5.0, 5.0, 5.0), 10 ** 6),
+                                            ((30, 18), (2.0, 3.0), 10 ** 6), ((64,), (7.0,), 10 ** 6), ((2, 2, 2), (1, 1, 1), 30)])
+def test_random_fields_vs_oracle_all_paths(sbx_lib, torch_cuda, shape, L, cutoff):
+    rng = np.random.default_rng(hash(shape) % 2 ** 32)
+    mats = [rng.standard_normal(shape) for _ in range(3)]
+    for path in (DENSE, GATHER):
+        out = run_scatter(sbx_lib, torch_cuda, mats, L, cutoff, 1e-12, path)
+        for b, mat in enumerate(mats):
+            ref, _ = scatter_np.scattering_peak_table(mat, L, cutoff, 1e-12)
+            qI = np.stack([out["q"], out["I"][b].cpu().numpy()], axis=1)
+            check_scatter_rows(qI, ref, cutoff, last_shell_members(mat, L, cutoff, 1e-12))
+
+
+def test_gather_path_is_bitwise_reproducible(sbx_lib, torch_cuda):
+    from simubox_b200 import synth
+
+    mats = [synth.field_numpy(i, (32, 32, 32)) for i in range(4)]
+    a = run_scatter(sbx_lib, torch_cuda, mats, synth.box_for(2), 30, 1e-12, GATHER)["I"].cpu().numpy()
+    b = run_scatter(sbx_lib, torch_cuda, mats[::-1], synth.box_for(2), 30, 1e-12, GATHER)["I"].cpu().numpy()
+    assert np.array_equal(a, b[::-1])
+
+
+def test_host_streaming_entry_point(sbx_lib, torch_cuda):
+    """sbx_scatter_execute_host: numpy in, numpy out, ragged last chunk, pinned and pageable input."""
+    from simubox_b200 import Scatter, synth
+
+    mats = np.stack([synth.field_numpy(i, (32, 32, 32)) for i in range(7)])
+    L = synth.box_for(2)
+    dev = run_scatter(sbx_lib, torch_cuda, list(mats), L, 30, 1e-12, GATHER, peaks=dict(width=0.5, step=2000, cutoff=20, min_height=1))
+    pinned = torch_cuda.from_numpy(mats).pin_memory()
+    for src in (mats, pinned):
+        out = Scatter.sacttering_peak_batch(src, L, peaks=True, max_batch=3, path=GATHER)
+        assert np.array_equal(out["I"], dev["I"].cpu().numpy())
+        assert np.array_equal(out["n_peaks"], dev["n_peaks"].cpu().numpy())
+        n = int(out["n_peaks"][0])
+        assert np.array_equal(out["peak_idx"][:, :n], dev["peak_idx"][:, :n].cpu().numpy())
+
+
+@pytest.mark.parametrize("n,cells", [(128, 2), (256, 4)])
+def test_properties_at_baseline_sizes(sbx_lib, torch_cuda, n, cells):
+    """Size-independent checks at the BASELINE grids (the numpy oracle needs minutes there):
+    DC row = (sum rho)^2/N; a periodic shift leaves every shell sum unchanged; scaling the field
+    by 2 scales I by exactly 4; dense and gather paths agree; first Bragg shells of the
+    gyroid/BCC fields carry the intensity."""
+    from simubox_b200 import Scatter, synth
+
+    torch = torch_cuda
+    L = synth.box_for(cells)
+    f = synth.fields_torch(0, 2, (n, n, n), cells=cells)
+    shifted = torch.roll(f, shifts=(5, n // 3, 1), dims=(1, 2, 3)).contiguous()
+    outs = {p: Scatter.sacttering_peak_batch(f, L, path=p, max_batch=2)["I"].cpu().numpy() for p in (DENSE, GATHER)}
+    tol = 1e-9 * np.abs(outs[GATHER]) + 1e-12 * np.abs(outs[GATHER]).max()
+    assert np.all(np.abs(outs[DENSE] - outs[GATHER]) <= tol)
+    I = outs[GATHER]
+    dc = (f.sum(dim=(1, 2, 3)) ** 2 / n ** 3).cpu().numpy()
+    assert np.allclose(I[:, 0], dc, rtol=1e-11)
+    Is = Scatter.sacttering_peak_batch(shifted, L, path=GATHER, max_batch=2)["I"].cpu().numpy()
+    assert np.all(np.abs(Is[:, :-1] - I[:, :-1]) <= 1e-9 * np.abs(I[:, :-1]) + 1e-12 * np.abs(I).max())
+    I2 = Scatter.sacttering_peak_batch(2.0 * f, L, path=GATHER, max_batch=2)["I"].cpu().numpy()
+    assert np.array_equal(I2, 4.0 * I)
+    # gyroid (field 0): first allowed reflection is {211} -> |k|^2 = 6 (2 pi cells / L)^2; BCC (field 1): {110} -> 2
+    q = Scatter.sacttering_peak_batch(f, L, path=GATHER, max_batch=2)["q"]
+    unit = 2 * np.pi * cells / L[0]
+    assert abs(q[1 + np.argmax(I[0, 1:])] / unit - np.sqrt(6)) < 1e-9
+    assert abs(q[1 + np.argmax(I[1, 1:])] / unit - np.sqrt(2)) < 1e-9

@@ -1,0 +1,80 @@
+"""CPU suite: oracle restatement vs the committed golden vectors (generated from the LIVE
+reference by oracle/make_golden.py), and -- when /root/reference is present -- vs the live
+reference itself."""
+import json
+
+import numpy as np
+import pytest
+
+from conftest import check_scatter_rows, golden, golden_field, golden_names
+from oracle import scatter_np, voronoi_np
+
+
+def last_shell_members(mat, L, cutoff, thr):
+    """Intensities of every mode in the (possibly truncated) last returned shell."""
+    k2, _ = scatter_np.mode_k2(mat.shape, L)
+    reps, _, trunc, _, _ = scatter_np.shell_table(mat.shape, L, cutoff, thr)
+    inten = np.abs(np.fft.fftn(mat) ** 2) / mat.size
+    sel = (k2 >= reps[-1]) & (np.abs(reps[-1] - k2) <= thr)
+    return inten[sel]
+
+
+@pytest.mark.parametrize("name", golden_names("scatter_"))
+def test_scatter_restatements_match_golden(name):
+    g = golden(name)
+    mat, L, cutoff, thr = golden_field(g), g["L"], int(g["cutoff"]), float(g["threshold"])
+    members = last_shell_members(mat, L, cutoff, thr)
+    for fn in (scatter_np.scattering_peak, scatter_np.scattering_peak_table):
+        qI, qidx = fn(mat, L, cutoff, thr)
+        check_scatter_rows(qI, g["q_Intensity"], cutoff, members)
+        counts = np.bincount(g["qidx_shell"], minlength=len(qI))
+        assert [len(qidx[s]) for s in range(len(qI))] == list(counts)
+        full = len(qI) - 1 if len(qI) == cutoff + 1 else len(qI)
+        for s in range(full):  # multiset of member vectors (order is sort-dependent, quirk Q3)
+            a = np.sort(np.stack(qidx[s]).view([("", float)] * mat.ndim), axis=0)
+            b = np.sort(np.ascontiguousarray(g["qidx_vec"][g["qidx_shell"] == s]).view([("", float)] * mat.ndim), axis=0)
+            assert np.array_equal(a, b)
+
+
+@pytest.mark.parametrize("name", [n for n in golden_names("scatter_") if "peaks_index" in golden(n).files])
+def test_show_peak_restatement_matches_golden(name):
+    g = golden(name)
+    kw = json.loads(str(g["peak_kw"]))
+    out = scatter_np.show_peak(g["q_Intensity"], **kw)
+    assert np.array_equal(out["peaks_index"], g["peaks_index"])
+    assert np.array_equal(out["plot_y"], g["plot_y"])
+    assert np.array_equal(out["plot_x"], g["plot_x"])
+    assert np.array_equal(out["peaks_location"], g["peaks_location"])
+    assert np.array_equal(scatter_np.find_peaks_height(g["plot_y"], kw["min_height"]), g["peaks_index"])
+
+
+@pytest.mark.parametrize("name", golden_names("vor"))
+def test_voronoi_restatement_matches_golden(name):
+    g = golden(name)
+    w = g["weights"] if g["weights"].ndim else float(g["weights"])
+    box = tuple(g["box"]) if g["box"].size else None
+    lab = voronoi_np.label_grid(g["points"], w, tuple(g["size"]), method=str(g["method"]), box=box)
+    assert np.array_equal(lab, g["labels"])
+
+
+def test_find_peaks_restatement_plateaus_and_edges():
+    import scipy.signal as sg
+
+    rng = np.random.default_rng(3)
+    for _ in range(200):
+        y = rng.integers(0, 4, size=rng.integers(3, 60)).astype(float)
+        ref, _ = sg.find_peaks(y, height=1.0)
+        assert np.array_equal(scatter_np.find_peaks_height(y, 1.0), ref)
+
+
+@pytest.mark.reference
+def test_live_reference_still_matches_goldens():
+    from oracle import ref_live
+
+    for name in ["scatter_random_8x12x10_c10", "scatter_phoutC6_t0_unitbox", "scatter_synth_16_f0"]:
+        g = golden(name)
+        qI, qidx, _ = ref_live.ref_scatter(golden_field(g), g["L"], cutoff=int(g["cutoff"]), threshold=float(g["threshold"]))
+        assert np.array_equal(qI[:-1], g["q_Intensity"][:-1])
+    g = golden("vor3d_periodic_w")
+    lab = ref_live.ref_label(g["points"], g["weights"], tuple(g["size"]), images=voronoi_np.image_offsets(g["box"]))
+    assert np.array_equal(lab, g["labels"])
