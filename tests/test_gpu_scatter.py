@@ -153,8 +153,8 @@ def test_properties_at_baseline_sizes(sbx_lib, torch_cuda, n, cells):
     assert np.all(np.abs(Is[:, :-1] - I[:, :-1]) <= 1e-9 * np.abs(I[:, :-1]) + 1e-12 * np.abs(I).max())
     I2 = Scatter.sacttering_peak_batch(2.0 * f, L, path=GATHER, max_batch=2)["I"].cpu().numpy()
     assert np.array_equal(I2, 4.0 * I)
-    # gyroid (field 0): first allowed reflection is {211} -> |k|^2 = 6 (2 pi cells / L)^2; BCC (field 1): {110} -> 2
+    # both level sets (sin X cos Y + ... / cos X cos Y + ...) are built from the {110} star: |k|^2 = 2 (2 pi cells / L)^2
     q = Scatter.sacttering_peak_batch(f, L, path=GATHER, max_batch=2)["q"]
     unit = 2 * np.pi * cells / L[0]
-    assert abs(q[1 + np.argmax(I[0, 1:])] / unit - np.sqrt(6)) < 1e-9
+    assert abs(q[1 + np.argmax(I[0, 1:])] / unit - np.sqrt(2)) < 1e-9
     assert abs(q[1 + np.argmax(I[1, 1:])] / unit - np.sqrt(2)) < 1e-9
