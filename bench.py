@@ -229,10 +229,13 @@ def run_scatter(args):
         last["out"] = Scatter.sacttering_peak_batch(fields, L, **kw)
 
     # --- device-resident throughput (inputs already in HBM; 4.3 GB per pass >> 126 MB L2, no flush needed)
-    with ClockSampler(local) as clk:
-        plan.set_profiling(False)
-        ms = timed_steps(step_device, args.steps, args.warmup, world, dev)
-    clocks = clk.summary()
+    clk = ClockSampler(local).__enter__()  # sampled across the device-timed, profiled and end-to-end regions
+    step_device()
+    t_wait = time.time()
+    while not clk.rows and time.time() - t_wait < 3.0:
+        time.sleep(0.05)
+    plan.set_profiling(False)
+    ms = timed_steps(step_device, args.steps, args.warmup, world, dev)
     # --- same steps again with per-stage CUDA events (transform vs hand-written kernel split)
     plan.set_profiling(True)
     plan.profile(reset=True)
@@ -249,8 +252,10 @@ def run_scatter(args):
     host.copy_(fields)
     torch.cuda.synchronize()
 
+    kw_host = dict(kw, max_batch=args.host_batch)
+
     def step_host():
-        last["host"] = Scatter.sacttering_peak_batch(host, L, **kw)
+        last["host"] = Scatter.sacttering_peak_batch(host, L, **kw_host)
 
     for _ in range(max(1, min(args.warmup, 2))):
         step_host()
@@ -260,6 +265,8 @@ def run_scatter(args):
         step_host()
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.e2e_steps, world, dev)
+    clk.__exit__()
+    clocks = clk.summary()
     ns = plan.n_shells
     h2d = B * n ** 3 * 8
     d2h = B * (ns * 8 + 4 + 256 * 4)
@@ -271,17 +278,21 @@ def run_scatter(args):
     spec_bytes = 16 * n * n * (n // 2 + 1)
     pipeline_bytes = 8 * n ** 3 + 2 * spec_bytes
     pathname = _lib.PATH_NAMES[plan.path]
-    if plan.path == 3:  # pruned DFT: the kernel reads each field once
-        kern, unit_bytes = "pruned_dft_kernel", 8 * n ** 3
+    if plan.path == 3:  # pruned DFT: pruned_planes_kernel reads each field exactly once (first event pair)
+        kern, unit_bytes = "pruned_planes_kernel", 8 * n ** 3
+        launches_per_step = own_per_step / 2
+        fused_ms_per_launch = prof["transform_ms"] / max(prof["own_launches"] / 2, 1)
     else:
         kern, unit_bytes = ("shell_histogram_kernel" if plan.path == 1 else "shell_gather_kernel"), spec_bytes
-    fields_per_launch = B / max(own_per_step, 1)
+        launches_per_step = own_per_step
+    fields_per_launch = B / max(launches_per_step, 1)
     achieved = unit_bytes * fields_per_launch / (fused_ms_per_launch * 1e-3) / 1e9 if fused_ms_per_launch > 0 else None
     roof = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "unit": "GB/s",
             "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
             "algorithmic_bytes_per_field": unit_bytes, "fields_per_launch": fields_per_launch,
             "kernel_ms_per_launch": fused_ms_per_launch,
-            "step_split_ms": {"transform(cuFFT)": transform_ms_per_step, "own_kernels": fused_ms_per_step},
+            "step_split_ms": ({"pruned_planes_kernel": transform_ms_per_step, "pruned_finish_kernel": fused_ms_per_step} if plan.path == 3
+                              else {"transform(cuFFT)": transform_ms_per_step, "own_kernels": fused_ms_per_step}),
             "pipeline": {"bytes_per_field": pipeline_bytes, "achieved": pipeline_bytes * B / (ms * 1e-3) / 1e9,
                          "frac": pipeline_bytes * B / (ms * 1e-3) / 1e9 / peak}}
 
@@ -304,7 +315,7 @@ def run_scatter(args):
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"{B} synthetic 3-component gyroid/BCC {n}^3 fp64 fields per GPU, scatter I(q) cutoff=30 + show_peak",
-                   "grid": [n, n, n], "fields_per_gpu": B, "path": pathname, "fft_chunk": os.environ.get("SBX_FFT_CHUNK", "auto"),
+                   "grid": [n, n, n], "fields_per_gpu": B, "path": pathname, "fields_per_launch": min(args.max_batch, B), "host_chunk": args.host_batch,
                    "l2": "inputs (4.3 GB per pass) exceed the 126 MB L2; no flush needed", "parallelism": f"fields sharded, {world} rank(s), no collective"},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "fields/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
                 "ms_per_step": e2e_ms, "h2d_GBps": h2d / (e2e_ms * 1e-3) / 1e9, "api": "Scatter.sacttering_peak_batch(pinned host tensor) -> sbx_scatter_execute_host"},
@@ -438,7 +449,7 @@ def run_reference(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="scatter", choices=["scatter", "voronoi"])
@@ -446,7 +457,8 @@ def main():
     ap.add_argument("--grid", type=int, default=128)
     ap.add_argument("--cells", type=int, default=2)
     ap.add_argument("--fields", type=int, default=256)
-    ap.add_argument("--max-batch", type=int, default=16)
+    ap.add_argument("--max-batch", type=int, default=64, help="fields per kernel launch (device-resident path)")
+    ap.add_argument("--host-batch", type=int, default=16, help="fields per H2D chunk of the host-streaming path")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-fields", type=int, default=0)
     ap.add_argument("--vgrid", type=int, default=256)

@@ -92,7 +92,8 @@ int sbx_scatter_plan_get_profile(sbx_scatter_plan* plan, double* transform_ms, d
                                  int64_t* own_launches, int64_t* transform_calls, int reset);
 
 /* fields: batch x prod(N) fp64, C order (= DensityParseResult.mat of each field);
- * shell_I: batch x n_shells fp64 = q_Intensity[:,1] per field.  batch <= max_batch. */
+ * shell_I: batch x n_shells fp64 = q_Intensity[:,1] per field.  Any batch >= 1: the plan works
+ * through it in chunks of max_batch (its workspace size). */
 int sbx_scatter_execute(sbx_scatter_plan* plan, const double* fields, int batch, double* shell_I,
                         void* stream);
 

@@ -3,6 +3,7 @@
 #include <cufft.h>
 
 #include <algorithm>
+#include <array>
 #include <cmath>
 #include <cstdlib>
 #include <cstring>
@@ -11,6 +12,7 @@
 #include <vector>
 
 #include "common.h"
+#include "pruned_dft.cuh"
 #include "scatter_kernels.cuh"
 #include "shell_table.h"
 
@@ -70,6 +72,18 @@ struct sbx_scatter_plan {
   int* d_shell_off = nullptr;
   unsigned int* d_tickets = nullptr;
   double2* d_spec = nullptr;
+  // pruned-DFT path
+  PrunedGeo pruned{};
+  double* d_tw2 = nullptr;
+  double* d_tw1 = nullptr;
+  double2* d_tw0 = nullptr;
+  int4* d_umodes = nullptr;
+  long long* d_memb_u = nullptr;
+  double* d_planes = nullptr;
+  int n_umodes = 0;
+  bool pruned_ok = false;
+  cudaStream_t s_aux = nullptr;
+  cudaEvent_t ev_planes[2] = {nullptr, nullptr}, ev_finish[2] = {nullptr, nullptr};
   std::map<int, cufftHandle> fft;  // batch -> plan
   int blocks_per_field = 1;
   int sm_count = 148;
@@ -181,6 +195,70 @@ static int build_device_tables(sbx_scatter_plan* p) {
   return SBX_OK;
 }
 
+// ---- pruned-DFT tables: which modes, and the twiddle B-fragments of pruned_dft.cuh --------
+static double cos2pi(long long j, long long n) { return (double)cosl(6.283185307179586476925286766559L * (long double)(j % n) / (long double)n); }
+static double sin2pi(long long j, long long n) { return (double)sinl(6.283185307179586476925286766559L * (long double)(j % n) / (long double)n); }
+
+static int build_pruned_tables(sbx_scatter_plan* p) {
+  const ShellTable& t = p->tab;
+  p->pruned_ok = false;
+  if (t.ndim != 3) return SBX_OK;
+  const int64_t N0 = t.N[0], N1 = t.N[1], N2 = t.N[2];
+  if (N1 % 8 || N1 < 16 || N2 < 16) return SBX_OK;
+  if (pruned_smem_bytes((int)N1, (int)N2) > 100 * 1024) return SBX_OK;
+  if (t.n_members() > (int64_t)1 << 16) return SBX_OK;
+  std::map<std::array<int64_t, 3>, int> index;
+  std::vector<int4> umodes;
+  std::vector<long long> memb;
+  for (int s = 0; s < t.n_shells(); ++s)
+    for (int64_t f : t.members[s]) {
+      int64_t c = f % N2, b = (f / N2) % N1, a = f / (N2 * N1);
+      int64_t fa = a <= N0 / 2 ? a : a - N0, fb = b <= N1 / 2 ? b : b - N1, fc = c <= N2 / 2 ? c : c - N2;
+      if (fc < 0 || (fc == 0 && (fb < 0 || (fb == 0 && fa < 0)))) { fa = -fa; fb = -fb; fc = -fc; }  // Hermitian mirror
+      if (fc > 7 || fc >= N2 / 2 || fb > 7 || fb < -7 || 2 * (fb < 0 ? -fb : fb) >= N1) return SBX_OK;  // outside the 8x8 tile
+      std::array<int64_t, 3> key{fa, fb, fc};
+      auto it = index.find(key);
+      if (it == index.end()) {
+        it = index.emplace(key, (int)umodes.size()).first;
+        umodes.push_back(make_int4((int)(((fa % N0) + N0) % N0), (int)fb, (int)fc, 0));
+      }
+      memb.push_back(it->second);
+    }
+  if (umodes.size() > 8192) return SBX_OK;
+  PrunedGeo& g = p->pruned;
+  g.N0 = (int)N0; g.N1 = (int)N1; g.N2 = (int)N2;
+  g.ks2 = (int)((N2 / 2 + 1 + 3) / 4);
+  g.ks1 = (int)(N1 / 4);
+  g.gstride = (int)N1 + 4;
+  std::vector<double> tw2((size_t)g.ks2 * 64, 0.0), tw1((size_t)2 * g.ks1 * 32, 0.0);
+  for (int s = 0; s < g.ks2; ++s)
+    for (int lane = 0; lane < 32; ++lane) {
+      const int64_t tt = 4 * s + (lane & 3), n = lane >> 2;
+      if (tt > N2 / 2) continue;
+      tw2[(size_t)s * 64 + lane] = cos2pi(n * tt, N2);
+      tw2[(size_t)s * 64 + 32 + lane] = sin2pi(n * tt, N2);
+    }
+  for (int s = 0; s < g.ks1; ++s)
+    for (int lane = 0; lane < 32; ++lane) {
+      const int64_t y = 4 * s + (lane & 3), b = lane >> 2;
+      tw1[(size_t)s * 32 + lane] = cos2pi(b * y, N1);
+      tw1[((size_t)g.ks1 + s) * 32 + lane] = sin2pi(b * y, N1);
+    }
+  std::vector<double2> tw0(N0);
+  for (int64_t j = 0; j < N0; ++j) tw0[j] = make_double2(cos2pi(j, N0), sin2pi(j, N0));
+  int rc;
+  if ((rc = upload(&p->d_tw2, tw2))) return rc;
+  if ((rc = upload(&p->d_tw1, tw1))) return rc;
+  if ((rc = upload(&p->d_tw0, tw0))) return rc;
+  if ((rc = upload(&p->d_umodes, umodes))) return rc;
+  if ((rc = upload(&p->d_memb_u, memb))) return rc;
+  g.tw2 = p->d_tw2;
+  g.tw1 = p->d_tw1;
+  p->n_umodes = (int)umodes.size();
+  p->pruned_ok = true;
+  return SBX_OK;
+}
+
 extern "C" int sbx_version(void) { return SBX_VERSION; }
 extern "C" const char* sbx_last_error(void) { return g_err; }
 
@@ -206,12 +284,19 @@ static void free_plan(sbx_scatter_plan* p) {
   cudaFree(p->d_rep); cudaFree(p->d_q); cudaFree(p->d_plane2); cudaFree(p->d_plane);
   cudaFree(p->d_kvlast); cudaFree(p->d_elem); cudaFree(p->d_shell_off); cudaFree(p->d_tickets);
   cudaFree(p->d_spec);
+  cudaFree(p->d_tw2); cudaFree(p->d_tw1); cudaFree(p->d_tw0); cudaFree(p->d_umodes); cudaFree(p->d_memb_u);
+  cudaFree(p->d_planes);
   for (int i = 0; i < 2; ++i) {
     cudaFree(p->d_stage[i]); cudaFree(p->d_out[i]); cudaFree(p->d_pidx[i]); cudaFree(p->d_npk[i]);
     if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
     if (p->ev_done[i]) cudaEventDestroy(p->ev_done[i]);
     if (p->ev_out[i]) cudaEventDestroy(p->ev_out[i]);
   }
+  for (int i = 0; i < 2; ++i) {
+    if (p->ev_planes[i]) cudaEventDestroy(p->ev_planes[i]);
+    if (p->ev_finish[i]) cudaEventDestroy(p->ev_finish[i]);
+  }
+  if (p->s_aux) cudaStreamDestroy(p->s_aux);
   if (p->s_copy) cudaStreamDestroy(p->s_copy);
   if (p->s_comp) cudaStreamDestroy(p->s_comp);
   delete p;
@@ -249,11 +334,18 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   cudaDeviceGetAttribute(&p->sm_count, cudaDevAttrMultiProcessorCount, device);
 
   const GridDev& g = p->grid;
-  if (path == SBX_SCATTER_AUTO)
-    path = (p->tab.n_members() * 4 <= g.nspec) ? SBX_SCATTER_FFT_GATHER : SBX_SCATTER_FFT_DENSE;
-  if (path != SBX_SCATTER_FFT_DENSE && path != SBX_SCATTER_FFT_GATHER) {
+  if ((rc = build_pruned_tables(p))) { free_plan(p); return rc; }
+  if (path == SBX_SCATTER_AUTO) {
+    if (p->pruned_ok && !getenv("SBX_NO_PRUNED")) path = SBX_SCATTER_PRUNED;
+    else path = (p->tab.n_members() * 4 <= g.nspec) ? SBX_SCATTER_FFT_GATHER : SBX_SCATTER_FFT_DENSE;
+  }
+  if (path == SBX_SCATTER_PRUNED && !p->pruned_ok) {
     free_plan(p);
-    return fail(SBX_EINVAL, "scatter path %d is not available in this build", path);
+    return fail(SBX_EINVAL, "pruned-DFT path needs a 3D grid (N1 %% 8 == 0, N1,N2 >= 16) whose shell modes have |k_y|,k_z <= 7");
+  }
+  if (path != SBX_SCATTER_FFT_DENSE && path != SBX_SCATTER_FFT_GATHER && path != SBX_SCATTER_PRUNED) {
+    free_plan(p);
+    return fail(SBX_EINVAL, "unknown scatter path %d", path);
   }
   p->path = path;
   if ((size_t)p->tab.n_shells() * 3 * sizeof(double) > kMaxDynSmem) {
@@ -266,14 +358,25 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   const size_t per_field = (size_t)g.nreal * 8 + (size_t)g.nspec * 16;
   size_t chunk = (size_t)64 << 20;
   chunk = std::max<size_t>(1, chunk / per_field);
+  if (path == SBX_SCATTER_FFT_GATHER) chunk = (size_t)max_batch;  // one CTA per field: launch many fields at once
   if (const char* e = getenv("SBX_FFT_CHUNK")) chunk = std::max(1, atoi(e));
   p->chunk = (int)std::min<size_t>(chunk, (size_t)max_batch);
+  if (path == SBX_SCATTER_PRUNED) p->chunk = max_batch;
   const long long want = (4LL * p->sm_count + p->chunk - 1) / p->chunk;
   long long bpf = std::max<long long>((g.nspec + 16383) / 16384, want);
   bpf = std::min<long long>(bpf, std::max<long long>(1, g.nspec / 256));
   p->blocks_per_field = (int)std::min<long long>(bpf, 65535);
 
-  cudaError_t e = cudaMalloc((void**)&p->d_spec, (size_t)p->chunk * g.nspec * sizeof(double2));
+  cudaError_t e = cudaSuccess;
+  if (path == SBX_SCATTER_PRUNED) {
+    e = cudaMalloc((void**)&p->d_planes, (size_t)2 * p->chunk * g.N0 * 256 * sizeof(double));
+    if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->s_aux, cudaStreamNonBlocking);
+    for (int i = 0; i < 2 && e == cudaSuccess; ++i) {
+      e = cudaEventCreateWithFlags(&p->ev_planes[i], cudaEventDisableTiming);
+      if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_finish[i], cudaEventDisableTiming);
+    }
+  }
+  else e = cudaMalloc((void**)&p->d_spec, (size_t)p->chunk * g.nspec * sizeof(double2));
   if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_tickets, (size_t)max_batch * sizeof(unsigned));
   if (e == cudaSuccess) e = cudaMemset(p->d_tickets, 0, (size_t)max_batch * sizeof(unsigned));
   if (e != cudaSuccess) {
@@ -281,7 +384,9 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
     return fail(e == cudaErrorMemoryAllocation ? SBX_ENOMEM : SBX_ECUDA, "plan allocation: %s", cudaGetErrorString(e));
   }
   cufftHandle h;
-  if ((rc = get_fft(p, p->chunk, &h))) { free_plan(p); return rc; }
+  if (path != SBX_SCATTER_PRUNED && (rc = get_fft(p, p->chunk, &h))) { free_plan(p); return rc; }
+  cudaFuncSetAttribute(pruned_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(pruned_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
@@ -348,7 +453,7 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
                        cudaStream_t st) {
   if (!p || !fields || !shell_I) return fail(SBX_EINVAL, "NULL argument");
   if (p->device == SBX_DEVICE_NONE) return fail(SBX_ENODEVICE, "geometry-only plan: no device to execute on");
-  if (batch < 1 || batch > p->max_batch) return fail(SBX_EINVAL, "batch %d outside 1..max_batch=%d", batch, p->max_batch);
+  if (batch < 1) return fail(SBX_EINVAL, "batch must be >= 1, got %d", batch);
   DeviceGuard guard(p->device);
   const GridDev& g = p->grid;
   const ShellDev& sh = p->shell;
@@ -356,6 +461,49 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
   int rc;
   if (do_peaks && (rc = check_peaks_args(ns, pp.step, pp.max_peaks))) return rc;
   const size_t smem_peaks = do_peaks ? (peaks_smem_doubles(ns, pp.step) + ns) * sizeof(double) : 0;
+  if (p->path == SBX_SCATTER_PRUNED) {
+    const size_t sm1 = pruned_smem_bytes(g.N1, g.N2);
+    const size_t need2 = ((size_t)p->n_umodes + 2 + 2 * (size_t)g.N0) * sizeof(double);
+    const size_t sm2 = (size_t)ns * sizeof(double) + std::max(need2, do_peaks ? peaks_smem_doubles(ns, pp.step) * sizeof(double) : 0);
+    if (sm2 > kMaxDynSmem) return fail(SBX_EINVAL, "pruned finish kernel needs %zu bytes of shared memory", sm2);
+    // The finish kernel (one CTA per field, latency bound) runs on an auxiliary stream so that it
+    // overlaps the bandwidth-bound planes kernel of the next chunk; plane buffers are double buffered.
+    // With profiling on, everything is serialised on `st` to time each kernel alone.
+    const bool overlap = !p->profiling && batch > p->chunk;
+    const size_t plane_doubles = (size_t)p->chunk * g.N0 * 256;
+    int i = 0;
+    for (int c0 = 0; c0 < batch; c0 += p->chunk, ++i) {
+      const int nb = std::min(p->chunk, batch - c0);
+      const int slot = overlap ? (i & 1) : 0;
+      double* planes_buf = p->d_planes + (size_t)slot * plane_doubles;
+      const long long planes = (long long)nb * g.N0;
+      const int grid1 = (int)std::min<long long>(planes, 2LL * p->sm_count);
+      if (overlap) SBX_CUDA(cudaStreamWaitEvent(st, p->ev_finish[slot], 0));
+      if (p->profiling) prof_event(p, st);
+      pruned_planes_kernel<<<grid1, 256, sm1, st>>>(fields + (size_t)c0 * g.nreal, p->pruned, nb, planes_buf);
+      if (p->profiling) prof_event(p, st);
+      cudaStream_t fs = st;
+      if (overlap) {
+        SBX_CUDA(cudaEventRecord(p->ev_planes[slot], st));
+        SBX_CUDA(cudaStreamWaitEvent(p->s_aux, p->ev_planes[slot], 0));
+        fs = p->s_aux;
+      }
+      pruned_finish_kernel<<<nb, 256, sm2, fs>>>(planes_buf, g.N0, g.factor, p->d_umodes, p->n_umodes, p->d_tw0,
+                                                 p->d_memb_u, p->d_shell_off, ns, shell_I + (size_t)c0 * ns,
+                                                 do_peaks ? 1 : 0, p->d_q, pp, plot_y ? plot_y + (size_t)c0 * pp.step : nullptr,
+                                                 peak_idx ? peak_idx + (size_t)c0 * pp.max_peaks : nullptr,
+                                                 n_peaks ? n_peaks + c0 : nullptr);
+      SBX_CUDA(cudaGetLastError());
+      if (overlap) SBX_CUDA(cudaEventRecord(p->ev_finish[slot], p->s_aux));
+      if (p->profiling) prof_event(p, st);
+      p->own_launches += 2;
+    }
+    if (overlap) {
+      SBX_CUDA(cudaStreamWaitEvent(st, p->ev_finish[0], 0));
+      SBX_CUDA(cudaStreamWaitEvent(st, p->ev_finish[1], 0));
+    }
+    return SBX_OK;
+  }
   for (int c0 = 0; c0 < batch; c0 += p->chunk) {
     const int nb = std::min(p->chunk, batch - c0);
     cufftHandle h;

@@ -199,6 +199,65 @@ shell_gather_kernel(const double2* __restrict__ spec, long long nspec, double fa
               n_peaks ? n_peaks + field : nullptr, smem + n_shells);
 }
 
+// ------------------------------------------------------------------------------------------
+// Pruned-DFT finish: stage 3 (x transform) of pruned_dft.cuh for the listed modes only, then
+// |F|^2/N, shell sums in fixed order (bitwise reproducible) and the peak search.  One block
+// per field; one thread per mode, so no cross-lane reduction is needed.
+// planes: [field][x][16][16] doubles written by pruned_planes_kernel.
+// ------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(256)
+pruned_finish_kernel(const double* __restrict__ planes, int N0, double factor, const int4* __restrict__ umodes,
+                     int n_umodes, const double2* __restrict__ tw0, const long long* __restrict__ memb_u,
+                     const int* __restrict__ shell_off, int n_shells, double* __restrict__ shell_I, int do_peaks,
+                     const double* __restrict__ q, PeakParams pp, double* __restrict__ plot_y,
+                     int32_t* __restrict__ peak_idx, int32_t* __restrict__ n_peaks) {
+  extern __shared__ double smem[];
+  double* row = smem;                     // n_shells
+  double* Iu = smem + n_shells;           // n_umodes   (region reused by the peak search afterwards)
+  double2* tw = reinterpret_cast<double2*>(Iu + n_umodes + ((n_shells + n_umodes) & 1));  // N0, 16-byte aligned
+  const int field = blockIdx.x, tid = threadIdx.x;
+  const int lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  for (int j = tid; j < N0; j += blockDim.x) tw[j] = tw0[j];
+  __syncthreads();
+  const double* fp = planes + (long long)field * N0 * 256;
+  for (int u = tid; u < n_umodes; u += blockDim.x) {
+    const int4 md = umodes[u];  // x = a index (0..N0-1), y = signed b, z = c
+    const int ab = md.y < 0 ? -md.y : md.y;
+    const int o_rc = md.z * 16 + ab, o_rs = o_rc + 8, o_sc = (8 + md.z) * 16 + ab, o_ss = o_sc + 8;
+    double fr = 0.0, fi = 0.0;
+    int j = 0;
+#pragma unroll 4
+    for (int x = 0; x < N0; ++x) {
+      const double* hp = fp + (long long)x * 256;
+      const double rc = hp[o_rc], rs = hp[o_rs], sc = hp[o_sc], ss = hp[o_ss];
+      const double hr = md.y >= 0 ? rc - ss : rc + ss;
+      const double hi = md.y >= 0 ? -(rs + sc) : rs - sc;
+      const double2 w = tw[j];  // (cos, sin)(2 pi a x / N0)
+      fr += hr * w.x + hi * w.y;
+      fi += hi * w.x - hr * w.y;
+      j += md.x;
+      if (j >= N0) j -= N0;
+    }
+    Iu[u] = factor * (fr * fr + fi * fi);
+  }
+  __syncthreads();
+  for (int s = warp; s < n_shells; s += nwarp) {
+    double acc = 0.0;
+    for (int m = shell_off[s] + lane; m < shell_off[s + 1]; m += 32) acc += Iu[memb_u[m]];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+      row[s] = acc;
+      shell_I[(long long)field * n_shells + s] = acc;
+    }
+  }
+  if (!do_peaks) return;
+  __syncthreads();
+  peaks_block(q, row, n_shells, pp, plot_y ? plot_y + (long long)field * pp.step : nullptr,
+              peak_idx ? peak_idx + (long long)field * pp.max_peaks : nullptr,
+              n_peaks ? n_peaks + field : nullptr, smem + n_shells);
+}
+
 // stand-alone peak search (sbx_peaks_execute): one block per field
 __global__ void __launch_bounds__(256)
 peaks_kernel(const double* __restrict__ q, const double* __restrict__ I, int n, PeakParams pp,

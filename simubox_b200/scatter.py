@@ -104,18 +104,11 @@ class Scatter:
             pidx = torch.empty((B, _MAX_PEAKS), dtype=torch.int32, device=f.device) if peaks else None
             npk = torch.empty((B,), dtype=torch.int32, device=f.device) if peaks else None
             st = stream_ptr(f.device.index)
-            nelem = int(np.prod(N))
-            for b0 in range(0, B, plan.max_batch):
-                nb = min(plan.max_batch, B - b0)
-                fp = C.c_void_p(f.data_ptr() + b0 * nelem * 8)
-                ip = C.c_void_p(I.data_ptr() + b0 * plan.n_shells * 8)
-                if peaks:
-                    _lib.check(L_.sbx_scatter_peaks_execute(
-                        plan.handle, fp, nb, ip, width, step, peak_cutoff, min_height, None,
-                        C.c_void_p(pidx.data_ptr() + b0 * _MAX_PEAKS * 4), C.c_void_p(npk.data_ptr() + b0 * 4),
-                        _MAX_PEAKS, st))
-                else:
-                    _lib.check(L_.sbx_scatter_execute(plan.handle, fp, nb, ip, st))
+            if peaks:
+                _lib.check(L_.sbx_scatter_peaks_execute(plan.handle, ptr(f), B, ptr(I), width, step, peak_cutoff,
+                                                        min_height, None, ptr(pidx), ptr(npk), _MAX_PEAKS, st))
+            else:
+                _lib.check(L_.sbx_scatter_execute(plan.handle, ptr(f), B, ptr(I), st))
             res["I"] = I
             if peaks:
                 res["peak_idx"], res["n_peaks"] = pidx, npk
