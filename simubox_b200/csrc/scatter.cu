@@ -75,6 +75,9 @@ struct sbx_scatter_plan {
   // pruned-DFT path
   PrunedGeo pruned{};
   double* d_tw2 = nullptr;
+  double* d_tw2f = nullptr;   // full-K stage-1 fragments (variant B), only when N2 % 8 == 0
+  int pruned_variant = 0;     // 0 = paired z / N2-z (variant A), 1 = full K with 16-byte loads (variant B)
+  int pruned_ctas_per_sm = 3;
   double* d_tw1 = nullptr;
   double2* d_tw0 = nullptr;
   int4* d_umodes = nullptr;
@@ -249,6 +252,21 @@ static int build_pruned_tables(sbx_scatter_plan* p) {
   int rc;
   if ((rc = upload(&p->d_tw2, tw2))) return rc;
   if ((rc = upload(&p->d_tw1, tw1))) return rc;
+  if (N2 % 8 == 0) {
+    std::vector<double> tw2f((size_t)(N2 / 8) * 128);
+    for (int64_t s = 0; s < N2 / 8; ++s)
+      for (int lane = 0; lane < 32; ++lane) {
+        const int64_t n = lane >> 2, te = 8 * s + 2 * (lane & 3), to = te + 1;
+        tw2f[(size_t)s * 128 + lane] = cos2pi(n * te, N2);
+        tw2f[(size_t)s * 128 + 32 + lane] = sin2pi(n * te, N2);
+        tw2f[(size_t)s * 128 + 64 + lane] = cos2pi(n * to, N2);
+        tw2f[(size_t)s * 128 + 96 + lane] = sin2pi(n * to, N2);
+      }
+    if ((rc = upload(&p->d_tw2f, tw2f))) return rc;
+    p->pruned_variant = 1;
+  }
+  if (const char* e = getenv("SBX_PRUNED_VARIANT")) p->pruned_variant = (atoi(e) == 1 && p->d_tw2f) ? 1 : 0;
+  if (const char* e = getenv("SBX_PRUNED_CTAS")) p->pruned_ctas_per_sm = std::max(1, std::min(3, atoi(e)));
   if ((rc = upload(&p->d_tw0, tw0))) return rc;
   if ((rc = upload(&p->d_umodes, umodes))) return rc;
   if ((rc = upload(&p->d_memb_u, memb))) return rc;
@@ -284,7 +302,7 @@ static void free_plan(sbx_scatter_plan* p) {
   cudaFree(p->d_rep); cudaFree(p->d_q); cudaFree(p->d_plane2); cudaFree(p->d_plane);
   cudaFree(p->d_kvlast); cudaFree(p->d_elem); cudaFree(p->d_shell_off); cudaFree(p->d_tickets);
   cudaFree(p->d_spec);
-  cudaFree(p->d_tw2); cudaFree(p->d_tw1); cudaFree(p->d_tw0); cudaFree(p->d_umodes); cudaFree(p->d_memb_u);
+  cudaFree(p->d_tw2); cudaFree(p->d_tw2f); cudaFree(p->d_tw1); cudaFree(p->d_tw0); cudaFree(p->d_umodes); cudaFree(p->d_memb_u);
   cudaFree(p->d_planes);
   for (int i = 0; i < 2; ++i) {
     cudaFree(p->d_stage[i]); cudaFree(p->d_out[i]); cudaFree(p->d_pidx[i]); cudaFree(p->d_npk[i]);
@@ -386,6 +404,7 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   cufftHandle h;
   if (path != SBX_SCATTER_PRUNED && (rc = get_fft(p, p->chunk, &h))) { free_plan(p); return rc; }
   cudaFuncSetAttribute(pruned_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(pruned_planes_fullk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
@@ -462,7 +481,7 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
   if (do_peaks && (rc = check_peaks_args(ns, pp.step, pp.max_peaks))) return rc;
   const size_t smem_peaks = do_peaks ? (peaks_smem_doubles(ns, pp.step) + ns) * sizeof(double) : 0;
   if (p->path == SBX_SCATTER_PRUNED) {
-    const size_t sm1 = pruned_smem_bytes(g.N1, g.N2);
+    const size_t sm1 = p->pruned_variant == 1 ? pruned_fullk_smem_bytes(g.N1, g.N2) : pruned_smem_bytes(g.N1, g.N2);
     const size_t need2 = ((size_t)p->n_umodes + 2 + 2 * (size_t)g.N0) * sizeof(double);
     const size_t sm2 = (size_t)ns * sizeof(double) + std::max(need2, do_peaks ? peaks_smem_doubles(ns, pp.step) * sizeof(double) : 0);
     if (sm2 > kMaxDynSmem) return fail(SBX_EINVAL, "pruned finish kernel needs %zu bytes of shared memory", sm2);
@@ -477,10 +496,13 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
       const int slot = overlap ? (i & 1) : 0;
       double* planes_buf = p->d_planes + (size_t)slot * plane_doubles;
       const long long planes = (long long)nb * g.N0;
-      const int grid1 = (int)std::min<long long>(planes, 2LL * p->sm_count);
+      const int grid1 = (int)std::min<long long>(planes, (long long)p->pruned_ctas_per_sm * p->sm_count);
       if (overlap) SBX_CUDA(cudaStreamWaitEvent(st, p->ev_finish[slot], 0));
       if (p->profiling) prof_event(p, st);
-      pruned_planes_kernel<<<grid1, 256, sm1, st>>>(fields + (size_t)c0 * g.nreal, p->pruned, nb, planes_buf);
+      if (p->pruned_variant == 1)
+        pruned_planes_fullk_kernel<<<grid1, 256, sm1, st>>>(fields + (size_t)c0 * g.nreal, p->pruned, p->d_tw2f, nb, planes_buf);
+      else
+        pruned_planes_kernel<<<grid1, 256, sm1, st>>>(fields + (size_t)c0 * g.nreal, p->pruned, nb, planes_buf);
       if (p->profiling) prof_event(p, st);
       cudaStream_t fs = st;
       if (overlap) {
@@ -488,7 +510,7 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
         SBX_CUDA(cudaStreamWaitEvent(p->s_aux, p->ev_planes[slot], 0));
         fs = p->s_aux;
       }
-      pruned_finish_kernel<<<nb, 256, sm2, fs>>>(planes_buf, g.N0, g.factor, p->d_umodes, p->n_umodes, p->d_tw0,
+      pruned_finish_kernel<<<nb, 1024, sm2, fs>>>(planes_buf, g.N0, g.factor, p->d_umodes, p->n_umodes, p->d_tw0,
                                                  p->d_memb_u, p->d_shell_off, ns, shell_I + (size_t)c0 * ns,
                                                  do_peaks ? 1 : 0, p->d_q, pp, plot_y ? plot_y + (size_t)c0 * pp.step : nullptr,
                                                  peak_idx ? peak_idx + (size_t)c0 * pp.max_peaks : nullptr,

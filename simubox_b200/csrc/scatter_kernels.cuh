@@ -205,7 +205,7 @@ shell_gather_kernel(const double2* __restrict__ spec, long long nspec, double fa
 // per field; one thread per mode, so no cross-lane reduction is needed.
 // planes: [field][x][16][16] doubles written by pruned_planes_kernel.
 // ------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(1024)
 pruned_finish_kernel(const double* __restrict__ planes, int N0, double factor, const int4* __restrict__ umodes,
                      int n_umodes, const double2* __restrict__ tw0, const long long* __restrict__ memb_u,
                      const int* __restrict__ shell_off, int n_shells, double* __restrict__ shell_I, int do_peaks,
