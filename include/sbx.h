@@ -136,9 +136,19 @@ int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seed
                       const uint8_t* mask, int32_t* labels, void* stream, int64_t* stats_host);
 
 /* ---- one giant field across GPUs: slab-decomposed FFT + NCCL all-to-all ---------------
- * nccl_comm: an ncclComm_t (as void*) spanning `world` ranks; local_slab = planes
- * [rank*N0/world, (rank+1)*N0/world) of the field; shell_I: n_shells fp64, identical on all
- * ranks after the call completes on `stream`. */
+ * The reference cannot run a 1024^3 field (scatter.py:82-97 materialises ~300 B/voxel); its only
+ * distributed FFT is the FFTW-MPI slab code of the detached solver
+ * (work/.../ABC_star/abc_star_short.c:270-286).  One process per GPU:
+ *   sbx_nccl_unique_id on rank 0 -> broadcast the SBX_NCCL_ID_BYTES bytes by any means
+ *   (torch.distributed, MPI, a file) -> sbx_nccl_comm_create on every rank.
+ * NCCL is loaded at run time with dlopen (the copy already in the process, else $SBX_NCCL_LIB,
+ * else libnccl.so.2).  N0 and N1 must be divisible by `world`.
+ * local_slab = planes [rank*N0/world, (rank+1)*N0/world) of the field (fp64, C order);
+ * shell_I: n_shells fp64, identical on all ranks after the call completes on `stream`. */
+#define SBX_NCCL_ID_BYTES 128
+int sbx_nccl_unique_id(void* id_host /* SBX_NCCL_ID_BYTES */);
+int sbx_nccl_comm_create(void** comm, const void* id_host, int rank, int world, int device);
+int sbx_nccl_comm_destroy(void* comm);
 int sbx_scatter_slab_plan_create(sbx_slab_plan** out, void* nccl_comm, int rank, int world,
                                  int device, const int64_t* N, const double* L, int cutoff,
                                  double threshold);
@@ -146,7 +156,16 @@ int sbx_scatter_slab_shells(const sbx_slab_plan* plan, int* n_shells, double* q_
                             int64_t* count_host);
 int sbx_scatter_slab_execute(sbx_slab_plan* plan, const double* local_slab, double* shell_I,
                              void* stream);
+/* stage timing of the last execute after set_profiling(1): ms4_host = [2D FFT + pack, all-to-all,
+ * 1D FFT, histogram + all-reduce]; synchronises on the last event */
+int sbx_scatter_slab_set_profiling(sbx_slab_plan* plan, int enable);
+int sbx_scatter_slab_profile(sbx_slab_plan* plan, double* ms4_host);
 int sbx_scatter_slab_plan_destroy(sbx_slab_plan* plan);
+/* The same decomposition for all `world` ranks on ONE device (device memcpys as the exchange):
+ * field = the whole N0 x N1 x N2 field.  Validation of the slab path without several GPUs;
+ * synchronises `stream`. */
+int sbx_scatter_slab_emulate(int device, int world, const int64_t* N, const double* L, int cutoff,
+                             double threshold, const double* field, double* shell_I, void* stream);
 
 #ifdef __cplusplus
 }

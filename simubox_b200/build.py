@@ -27,6 +27,22 @@ def is_stale() -> bool:
     return any(p.stat().st_mtime > t for p in deps)
 
 
+def nccl_include() -> str:
+    """Directory holding nccl.h (types only: the library itself is dlopen'ed at run time)."""
+    try:
+        import nvidia.nccl as _n
+
+        for base in list(getattr(_n, "__path__", [])):
+            if (Path(base) / "include" / "nccl.h").exists():
+                return str(Path(base) / "include")
+    except Exception:
+        pass
+    for cand in ("/usr/include", "/usr/local/cuda/include"):
+        if (Path(cand) / "nccl.h").exists():
+            return cand
+    raise RuntimeError("nccl.h not found (needed for the slab-decomposed scatter types)")
+
+
 def build(force: bool = False, verbose: bool = False) -> Path:
     if not force and not is_stale():
         return LIB
@@ -37,7 +53,7 @@ def build(force: bool = False, verbose: bool = False) -> Path:
         "-O3", "-lineinfo", "-std=c++17",
         "-Xcompiler", "-fPIC,-O2,-ffp-contract=off",
         "-Xptxas", "-v" if verbose else "-O3",
-        "-lcufft", "-ldl",
+        "-I", nccl_include(), "-lcufft", "-ldl",
     ]
     res = subprocess.run(cmd, capture_output=True, text=True)
     if res.returncode != 0:

@@ -49,6 +49,20 @@ static int upload(T** dptr, const std::vector<T>& h) {
   return SBX_OK;
 }
 
+int launch_shell_histogram3(const double2* spec, const GridDev& g, const ShellDev& sh, double* shell_I, int blocks,
+                            cudaStream_t st) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    cudaFuncSetAttribute(shell_histogram_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, 200 * 1024);
+    attr_set = true;
+  }
+  PeakParams pp{};
+  shell_histogram_kernel<3><<<dim3(blocks, 1), 256, (size_t)2 * sh.n_shells * sizeof(double), st>>>(
+      spec, g, sh, shell_I, nullptr, 0, nullptr, pp, nullptr, nullptr, nullptr);
+  SBX_CUDA(cudaGetLastError());
+  return SBX_OK;
+}
+
 }  // namespace sbx
 
 using namespace sbx;
@@ -146,6 +160,8 @@ static int build_device_tables(sbx_scatter_plan* p) {
   g.nreal = t.total();
   g.nspec = g.nreal / nlast * g.H;
   g.factor = 1.0 / (double)g.nreal;
+  g.n1loc = g.N1;
+  g.joff = 0;
   int rc;
   if (t.ndim == 3) {
     const int64_t rows = t.N[0] * t.N[1];

@@ -11,29 +11,9 @@
 #include <cuda_runtime.h>
 
 #include "peaks.cuh"
+#include "scatter_types.h"
 
 namespace sbx {
-
-struct ShellDev {
-  const double* rep;  // n_shells ascending k^2 of each shell's first member
-  int n_shells;
-  int truncated;       // last shell keeps only `designated`
-  long long designated;
-  double threshold;
-  double vcut;  // conservative upper bound: k^2 > vcut can never be binned
-};
-
-struct GridDev {
-  int ndim;
-  int N0, N1, N2;      // unused trailing dims = 1
-  int H;               // stored length of the last axis = N_last/2 + 1
-  long long nspec;     // stored elements per field
-  long long nreal;     // real samples per field
-  const double2* plane2;  // 3D: per (a,b) row {plane k^2 of F[a,b,.], plane k^2 of its mirror row}
-  const double* plane;    // 1D/2D: k^2 per full-spectrum position (N0 or N0*N1 entries)
-  const double* kvlast;   // 3D: kv2[c], c < H
-  double factor;          // 1 / prod(N)  (scatter.py:84)
-};
 
 // largest s with rep[s] <= v (v >= rep[0] = smallest k^2 of the grid)
 __device__ __forceinline__ int shell_search(const double* rep, int n, double v) {
@@ -93,8 +73,13 @@ shell_histogram_kernel(const double2* __restrict__ spec, GridDev g, ShellDev sh,
     long long f1, f2;
     bool has_mirror;
     if (NDIM == 3) {
-      const long long row = e / g.H;
-      const int c = (int)(e - row * g.H);
+      const long long lrow = e / g.H;
+      const int c = (int)(e - lrow * g.H);
+      long long row = lrow;
+      if (g.n1loc != g.N1) {  // slab layout [x][j_local][c] (slab.cu): global row = x*N1 + joff + j_local
+        const long long x = lrow / g.n1loc;
+        row = x * g.N1 + g.joff + (lrow - x * g.n1loc);
+      }
       const double2 p2 = g.plane2[row];
       if (fmin(p2.x, p2.y) > sh.vcut) continue;  // whole row beyond the table: never loaded
       const double kc = g.kvlast[c];

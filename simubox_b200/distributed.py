@@ -1,0 +1,213 @@
+"""Multi-GPU host logic: one process per GPU (``torch.distributed`` is the plumbing only).
+
+Two cases:
+
+* batches / sweeps of independent fields -- ``shard_range`` / ``shard_indices`` give each rank its
+  fields, ``gather_rows`` brings the small per-field results to every rank.  No data-path
+  collective.
+* one giant field -- ``SlabScatter`` owns an NCCL communicator created by libsimubox_b200.so
+  (``sbx_nccl_unique_id`` on rank 0, broadcast through the existing process group,
+  ``sbx_nccl_comm_create`` everywhere) and runs the slab-decomposed FFT with an all-to-all
+  (``sbx_scatter_slab_execute``, csrc/slab.cu).
+"""
+from __future__ import annotations
+
+import ctypes as C
+import os
+from typing import Sequence, Tuple
+
+import numpy as np
+
+from . import _lib
+
+
+def rank_world() -> Tuple[int, int]:
+    """(rank, world) from an initialised process group, else from the torchrun environment."""
+    try:
+        import torch.distributed as dist
+
+        if dist.is_available() and dist.is_initialized():
+            return dist.get_rank(), dist.get_world_size()
+    except Exception:
+        pass
+    return int(os.environ.get("RANK", "0")), int(os.environ.get("WORLD_SIZE", "1"))
+
+
+def shard_indices(total: int, rank: int, world: int) -> np.ndarray:
+    """Round-robin sharding of a sweep: field i goes to rank ``i % world``."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world {world}")
+    return np.arange(rank, int(total), world, dtype=np.int64)
+
+
+def shard_range(total: int, rank: int, world: int) -> Tuple[int, int]:
+    """Contiguous sharding: rank r owns [lo, hi); the first ``total % world`` ranks get one extra."""
+    if not (0 <= rank < world):
+        raise ValueError(f"rank {rank} outside world {world}")
+    base, extra = divmod(int(total), world)
+    lo = rank * base + min(rank, extra)
+    return lo, lo + base + (1 if rank < extra else 0)
+
+
+def slab_planes(N0: int, rank: int, world: int) -> Tuple[int, int]:
+    """Planes [lo, hi) of axis 0 owned by ``rank`` in the slab decomposition (N0 % world == 0)."""
+    if N0 % world:
+        raise ValueError(f"N0={N0} must be divisible by the number of ranks ({world})")
+    n0 = N0 // world
+    return rank * n0, (rank + 1) * n0
+
+
+def gather_rows(local_rows: np.ndarray, indices: Sequence[int], total: int) -> np.ndarray:
+    """All-gather per-field result rows (small: ~0.5 kB per field) into a (total, width) array on
+    every rank.  ``indices`` are the global field numbers of ``local_rows``.  Works on any
+    backend (gloo on CPU, nccl on GPU); with no process group it is the identity."""
+    import torch
+    import torch.distributed as dist
+
+    local_rows = np.ascontiguousarray(local_rows, dtype=np.float64)
+    if local_rows.ndim == 1:
+        local_rows = local_rows[:, None]
+    width = local_rows.shape[1]
+    out = np.zeros((int(total), width), dtype=np.float64)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        out[np.asarray(indices, dtype=np.int64)] = local_rows
+        return out
+    world = dist.get_world_size()
+    per = (int(total) + world - 1) // world
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    rows = torch.zeros((per, width), dtype=torch.float64, device=dev)
+    idx = torch.full((per,), -1, dtype=torch.int64, device=dev)
+    n = len(indices)
+    rows[:n] = torch.from_numpy(local_rows).to(dev)
+    idx[:n] = torch.as_tensor(np.asarray(indices, dtype=np.int64)).to(dev)
+    all_rows = [torch.empty_like(rows) for _ in range(world)]
+    all_idx = [torch.empty_like(idx) for _ in range(world)]
+    dist.all_gather(all_rows, rows)
+    dist.all_gather(all_idx, idx)
+    for r, i in zip(all_rows, all_idx):
+        i = i.cpu().numpy()
+        keep = i >= 0
+        out[i[keep]] = r.cpu().numpy()[keep]
+    return out
+
+
+def _nccl_library_hint():
+    """Point the dlopen in csrc/slab.cu at torch's bundled NCCL when nothing else is set."""
+    if os.environ.get("SBX_NCCL_LIB"):
+        return
+    try:
+        import nvidia.nccl as n
+
+        for base in list(getattr(n, "__path__", [])):
+            cand = os.path.join(base, "lib", "libnccl.so.2")
+            if os.path.exists(cand):
+                os.environ["SBX_NCCL_LIB"] = cand
+                return
+    except Exception:
+        pass
+
+
+class SlabScatter:
+    """Scattering rows of ONE field spread over the ranks of the current process group."""
+
+    def __init__(self, N, L, cutoff: int = 30, threshold: float = 1e-12, device: int | None = None):
+        import torch
+        import torch.distributed as dist
+
+        self.rank, self.world = rank_world()
+        self.device = int(device if device is not None else os.environ.get("LOCAL_RANK", "0"))
+        self.N = tuple(int(n) for n in N)
+        if len(self.N) != 3:
+            raise ValueError("the slab decomposition is for 3D fields")
+        L_ = _lib.lib()
+        self._comm = C.c_void_p()
+        self._h = C.c_void_p()
+        if self.world > 1:
+            if not (dist.is_available() and dist.is_initialized()):
+                raise RuntimeError("SlabScatter with WORLD_SIZE > 1 needs torch.distributed.init_process_group first")
+            _nccl_library_hint()
+            ident = [None]
+            if self.rank == 0:
+                buf = (C.c_char * 128)()
+                _lib.check(L_.sbx_nccl_unique_id(buf))
+                ident[0] = bytes(buf.raw)
+            dist.broadcast_object_list(ident, src=0)
+            buf = (C.c_char * 128).from_buffer_copy(ident[0])
+            torch.cuda.set_device(self.device)
+            _lib.check(L_.sbx_nccl_comm_create(C.byref(self._comm), buf, self.rank, self.world, self.device))
+        _, pn = _lib.i64(self.N)
+        _, pl = _lib.f64([float(l) for l in L])
+        _lib.check(L_.sbx_scatter_slab_plan_create(C.byref(self._h), self._comm, self.rank, self.world, self.device,
+                                                   pn, pl, int(cutoff), float(threshold)))
+        n = C.c_int()
+        _lib.check(L_.sbx_scatter_slab_shells(self._h, C.byref(n), None, None))
+        self.n_shells = n.value
+        self.q = np.empty(self.n_shells)
+        self.count = np.empty(self.n_shells, dtype=np.int64)
+        _lib.check(L_.sbx_scatter_slab_shells(self._h, C.byref(n), self.q.ctypes.data_as(C.POINTER(C.c_double)),
+                                              self.count.ctypes.data_as(C.POINTER(C.c_int64))))
+        self.planes = slab_planes(self.N[0], self.rank, self.world)
+
+    def execute(self, local_slab, out=None):
+        """``local_slab``: CUDA fp64 tensor (N0/world, N1, N2) = this rank's planes.  Returns the
+        (n_shells,) CUDA tensor of shell intensities (identical on every rank); asynchronous on
+        the current stream."""
+        import torch
+
+        lo, hi = self.planes
+        want = (hi - lo, self.N[1], self.N[2])
+        if tuple(local_slab.shape) != want or local_slab.dtype != torch.float64 or not local_slab.is_cuda:
+            raise ValueError(f"local_slab must be a CUDA float64 tensor of shape {want}")
+        slab = local_slab.contiguous()
+        if out is None:
+            out = torch.empty(self.n_shells, dtype=torch.float64, device=slab.device)
+        st = C.c_void_p(torch.cuda.current_stream(slab.device).cuda_stream)
+        _lib.check(_lib.lib().sbx_scatter_slab_execute(self._h, C.c_void_p(slab.data_ptr()), C.c_void_p(out.data_ptr()), st))
+        return out
+
+    def q_intensity(self, local_slab) -> np.ndarray:
+        """(n_shells, 2) array [q, I] like ``ScatterResult.q_Intensity``."""
+        I = self.execute(local_slab).cpu().numpy()
+        return np.stack([self.q, I], axis=1)
+
+    def set_profiling(self, enable: bool):
+        _lib.check(_lib.lib().sbx_scatter_slab_set_profiling(self._h, int(enable)))
+
+    def profile(self) -> dict:
+        ms = (C.c_double * 4)()
+        _lib.check(_lib.lib().sbx_scatter_slab_profile(self._h, ms))
+        return dict(fft2d_pack_ms=ms[0], all_to_all_ms=ms[1], fft1d_ms=ms[2], histogram_allreduce_ms=ms[3])
+
+    def close(self):
+        L_ = _lib.lib()
+        if self._h:
+            L_.sbx_scatter_slab_plan_destroy(self._h)
+            self._h = C.c_void_p()
+        if self._comm:
+            L_.sbx_nccl_comm_destroy(self._comm)
+            self._comm = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def slab_emulate(field, L, world: int, cutoff: int = 30, threshold: float = 1e-12, device: int = 0) -> np.ndarray:
+    """Run the ``world``-rank slab decomposition on ONE GPU (``sbx_scatter_slab_emulate``): the
+    single-device check of csrc/slab.cu.  ``field``: full (N0, N1, N2) fp64 array or CUDA tensor.
+    Returns the (n_shells,) intensities as numpy."""
+    from ._device import ptr, stream_ptr, to_device, torch_cuda
+
+    torch = torch_cuda()
+    f = to_device(field, device, torch.float64)
+    N = tuple(int(n) for n in f.shape)
+    plan = _lib.ScatterPlan(N, L, cutoff, threshold, 1, _lib.SBX_DEVICE_NONE)
+    out = torch.empty(plan.n_shells, dtype=torch.float64, device=f.device)
+    _, pn = _lib.i64(N)
+    _, pl = _lib.f64([float(l) for l in L])
+    _lib.check(_lib.lib().sbx_scatter_slab_emulate(device, int(world), pn, pl, int(cutoff), float(threshold), ptr(f), ptr(out),
+                                                   stream_ptr(device)))
+    plan.close()
+    return out.cpu().numpy()
