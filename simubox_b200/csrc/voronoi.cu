@@ -2,19 +2,23 @@
 //
 // Replaces the per-pixel Python loop of VoronoiCell.weighted_voronoi_diagrams
 // (SimuBox/calculator/voronoi.py:284-292) with VoronoiCell.additive (:244-246) or
-// VoronoiCell.power (:249-255) as the distance.  Three kernels:
-//   1. candidates_kernel<ND,0>: per COARSE tile (4 fine tiles per axis) the seeds that can win
-//      anywhere inside it, out of all S seeds;
-//   2. candidates_kernel<ND,1>: per FINE tile (8x8x8 voxels, 16x32 pixels) the possible winners
-//      out of the parent's list -- exact interval bounds with slack, never prunes a possible
-//      winner, ascending seed index -- written as staged records;
-//   3. label_tiles_kernel: stages the tile's records in shared memory with a TMA bulk copy
-//      (cp.async.bulk + mbarrier) and evaluates the reference expression per voxel in fp64 with
-//      round-to-nearest intrinsics (no FMA contraction); first minimum wins (np.argmin).
-// Periodic boxes use the minimum image per axis, which equals the minimum over the 3^d
-// replicated images of the reference expression because every fp64 step is monotone.  When
-// one image is nearest for the whole tile (the usual case) the record stores fl(p + m L) and the
-// per-voxel work is three subtractions and a sum of squares.
+// VoronoiCell.power (:249-255) as the distance.  The grid is always handled as three internal
+// axes (a 2D image is 1 x X x Y); three kernels:
+//   1. coarse_kernel: per COARSE tile (32^3 voxels / 256^2 pixels) the seeds that can win anywhere
+//      inside it, out of all S seeds (interval bounds with slack, ascending seed index);
+//   2. mid_kernel: one warp per MID tile (16^3 / 64^2) filters its parent's list and writes staged
+//      records: fl(p + m L) of the single periodic image that is nearest for the whole tile;
+//   3. label_kernel: one CTA per mid tile.  The records arrive in shared memory by TMA bulk copy
+//      (cp.async.bulk + mbarrier).  Every warp owns a 4x8x8 (1x32x8) sub-tile, prunes the list once
+//      more -- for unweighted seeds with the exact bisector test (d_B^2 - d_A^2 is affine in x, so its
+//      minimum over a box sits on a corner) -- and keeps the survivors as ballot bit masks.  Every
+//      thread owns a column of 8 voxels along the last axis: (dx^2 + dy^2) is formed once per
+//      candidate and dz^2 added per voxel, in the reference's summation order, with round-to-nearest
+//      intrinsics (no FMA contraction).  First minimum wins (np.argmin).
+// Periodic boxes use the minimum image per axis, which equals the minimum over the 3^d replicated
+// images of the reference expression because every fp64 step is monotone.  Tiles where no single
+// image is nearest everywhere (tiny boxes), power mode, and tiles whose candidate list overflows
+// fall back to a generic per-voxel evaluation of all three images per axis.
 #include <cstdint>
 #include <cuda_runtime.h>
 
@@ -22,67 +26,80 @@
 
 namespace sbx {
 
-constexpr int kCap = 64;          // candidate records staged per fine tile
-constexpr int kCoarseCap = 1024;  // candidate indices kept per coarse tile
-constexpr int kCF = 4;            // fine tiles per coarse tile and axis
-constexpr int kTileVox = 512;     // voxels (= threads) per fine tile
-constexpr int kFlagGeneric = 1 << 30;  // fine tile needs the generic 3-image evaluation
+constexpr int kCap = 128;          // candidate records staged per mid tile
+constexpr int kCoarseCap = 1024;   // candidate indices kept per coarse tile
+constexpr int kCol = 8;            // voxels per thread along the last axis
+constexpr int kFlagGeneric = 1 << 30;  // mid tile needs the generic 3-image evaluation
+constexpr unsigned kFull = 0xffffffffu;
 
 struct VorGeo {
-  int ndim;
-  int N[3];       // grid (ndim entries used)
-  int T[3];       // fine tile extent per axis
-  int nt[3];      // fine tiles per axis
-  int ct[3];      // coarse tiles per axis
+  int nd;         // real dimensions (2 or 3); internal axis 0 is a dummy of extent 1 when nd == 2
+  int N[3];       // grid, internal axes
+  int M[3];       // mid tile extent per axis
+  int C[3];       // coarse tile extent per axis
+  int nm[3];      // mid tiles per axis
+  int nc[3];      // coarse tiles per axis
   int periodic;
   int mode;       // 0 additive, 1 power
-  double box[3];
+  double box[3];  // internal axes
   long long S;
 };
 
 struct alignas(16) SeedRec { double x, y, z, w; };
 
-__device__ __forceinline__ void tile_coords(const int n[3], int ndim, int tile, int t[3]) {
-  for (int a = ndim - 1; a >= 0; --a) {
+__device__ __forceinline__ void tile_coords(const int n[3], int tile, int t[3]) {
+  for (int a = 2; a >= 0; --a) {
     t[a] = tile % n[a];
     tile /= n[a];
   }
 }
 
-// conservative per-axis distance interval between coordinate p and voxel range [lo, hi]
-__device__ __forceinline__ void axis_bounds(double p, double lo, double hi, double& dmin, double& dmax) {
-  dmin = fmax(0.0, fmax(lo - p, p - hi));
-  dmax = fmax(fabs(p - lo), fabs(p - hi));
+// seed coordinate on internal axis a (a >= 3 - ND)
+template <int ND>
+__device__ __forceinline__ double seed_coord(const double* __restrict__ seeds, long long s, int a) {
+  return seeds[s * ND + (a - (3 - ND))];
 }
 
-// bounds of the seed's value over the voxel box [lo, hi]; for periodic additive tiles also
-// reports per axis which image is nearest everywhere in the box (img[a] in -1..1), or sets
-// `ambiguous` when no single image is.
+// Conservative bounds of the seed's value over the voxel box [lo, hi] (internal axes, doubles).
+// pr[] receives the coordinate of the periodic image nearest to the box centre (fl(p +- L), the
+// number the reference evaluates); `amb` is set when some other image may be nearer for a voxel of
+// the box -- the bounds then cover all three images.
 template <int ND>
 __device__ __forceinline__ void seed_bounds(const VorGeo& g, const double* __restrict__ seeds,
-                                            const double* __restrict__ weights, long long s, const int lo[3],
-                                            const int hi[3], double& LB, double& UB, int img[3], bool& ambiguous) {
+                                            const double* __restrict__ weights, long long s, const double lo[3],
+                                            const double hi[3], double& LB, double& UB, double pr[3], bool& amb) {
   double smin = 0.0, smax = 0.0;
-  ambiguous = false;
+  amb = false;
+  pr[0] = 0.0;
 #pragma unroll
-  for (int a = 0; a < ND; ++a) {
-    double p = seeds[s * ND + a];
+  for (int a = 3 - ND; a < 3; ++a) {
+    const double p0 = seed_coord<ND>(seeds, s, a);
+    double p = p0;
     if (g.mode == 1) p += (double)s;  // voronoi.py:251 adds the seed index to every coordinate
-    double dmin, dmax;
-    axis_bounds(p, (double)lo[a], (double)hi[a], dmin, dmax);
-    img[a] = 0;
+    double q = p;
+    const double L = g.box[a];
     if (g.periodic) {
-      double n0, n1, p0, p1;
-      axis_bounds(p - g.box[a], (double)lo[a], (double)hi[a], n0, n1);
-      axis_bounds(p + g.box[a], (double)lo[a], (double)hi[a], p0, p1);
-      // nearest image = smallest worst-case distance; unambiguous if the others are farther everywhere
-      double bmax = dmax, o1 = n0, o2 = p0;
-      if (n1 < bmax) { bmax = n1; img[a] = -1; o1 = dmin; o2 = p0; }
-      if (p1 < bmax) { bmax = p1; img[a] = 1; o1 = dmin; o2 = n0; }
-      const double margin = 1e-9 * (bmax + 1.0);
-      if (!(fmin(o1, o2) > bmax + margin)) ambiguous = true;
-      dmin = fmin(dmin, fmin(n0, p0));
-      dmax = bmax;
+      const double d = p - 0.5 * (lo[a] + hi[a]);
+      if (d > 0.5 * L) { q = p - L; pr[a] = __dsub_rn(p0, L); }
+      else if (d < -0.5 * L) { q = p + L; pr[a] = __dadd_rn(p0, L); }
+      else pr[a] = p0;
+    } else {
+      pr[a] = p0;
+    }
+    const double u = lo[a] - q, v = q - hi[a];
+    double dmin = fmax(0.0, fmax(u, v));
+    double dmax = fmax(-u, -v);
+    if (g.periodic && !(dmax < 0.5 * L - 1e-9 * (L + 1.0))) {
+      amb = true;  // all three images of the reference: smallest lower bound, smallest upper bound
+      const double qs[3] = {p - L, p, p + L};
+      dmin = INFINITY;
+      dmax = INFINITY;
+#pragma unroll
+      for (int i = 0; i < 3; ++i) {
+        const double uu = lo[a] - qs[i], vv = qs[i] - hi[a];
+        dmin = fmin(dmin, fmax(0.0, fmax(uu, vv)));
+        dmax = fmin(dmax, fmax(-uu, -vv));
+      }
     }
     smin += dmin * dmin;
     smax += dmax * dmax;
@@ -90,6 +107,11 @@ __device__ __forceinline__ void seed_bounds(const VorGeo& g, const double* __res
   const double w = weights ? weights[s] : 0.0;
   if (g.mode == 0) { LB = sqrt(smin) - w; UB = sqrt(smax) - w; }
   else { LB = smin - w; UB = smax - w; }
+}
+
+__device__ __forceinline__ bool may_win(double LB, double U) {
+  const double slack = 1e-10 * (fabs(U) + fabs(LB) + 1.0);
+  return LB - slack <= U + slack;  // never drops a seed that could tie or win
 }
 
 // ---- mbarrier / TMA bulk copy helpers (PTX; SASS: SYNCS.* / UBLKCP) --------------------------
@@ -121,170 +143,225 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
 }
 
-// ------------------------------------------------------------------------------------------
-// Candidate selection.  LEVEL 0: one block per coarse tile, source = all seeds, output = seed
-// indices.  LEVEL 1: one block per fine tile, source = the parent's list (or all seeds if the
-// parent overflowed), output = staged records + indices.  A seed is kept iff its lower bound
-// over the tile does not exceed the smallest upper bound of any seed (with slack), so a seed
-// that wins or ties anywhere in the tile is never dropped.  Output order = ascending seed index.
-// ------------------------------------------------------------------------------------------
-template <int ND, int LEVEL>
-__global__ void __launch_bounds__(LEVEL == 0 ? 256 : 128)
-candidates_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
-                  int* __restrict__ clist, int* __restrict__ ccount,           // coarse lists (out for LEVEL 0, in for 1)
-                  SeedRec* __restrict__ rec, int* __restrict__ ridx, int* __restrict__ rcount) {
-  constexpr int NW = (LEVEL == 0 ? 256 : 128) / 32;
-  const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int lo[3] = {0, 0, 0}, hi[3] = {0, 0, 0}, t[3] = {0, 0, 0};
-  const int* src = nullptr;
-  long long n_src = g.S;
-  if (LEVEL == 0) {
-    tile_coords(g.ct, ND, tile, t);
-    for (int a = 0; a < ND; ++a) {
-      lo[a] = t[a] * g.T[a] * kCF;
-      hi[a] = min(lo[a] + g.T[a] * kCF, g.N[a]) - 1;
-    }
-  } else {
-    tile_coords(g.nt, ND, tile, t);
-    int parent = 0;
-    for (int a = 0; a < ND; ++a) {
-      lo[a] = t[a] * g.T[a];
-      hi[a] = min(lo[a] + g.T[a], g.N[a]) - 1;
-      parent = parent * g.ct[a] + t[a] / kCF;
-    }
-    const int pc = ccount[parent];
-    if (pc <= kCoarseCap) {
-      src = clist + (long long)parent * kCoarseCap;
-      n_src = pc;
-    }
-  }
-
-  __shared__ double s_red[NW];
-  __shared__ double s_U;
-  __shared__ int s_warp[NW];
-  __shared__ int s_total;
-  __shared__ int s_flag;
-  int img[3];
-  bool amb;
-  double best = INFINITY;
-  for (long long i = tid; i < n_src; i += blockDim.x) {
-    const long long s = src ? src[i] : i;
-    double LB, UB;
-    seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, img, amb);
-    best = fmin(best, UB);
-  }
-  for (int o = 16; o > 0; o >>= 1) best = fmin(best, __shfl_xor_sync(0xffffffffu, best, o));
-  if (lane == 0) s_red[warp] = best;
-  if (tid == 0) { s_total = 0; s_flag = 0; }
-  __syncthreads();
-  if (tid == 0) {
-    double u = s_red[0];
-    for (int w = 1; w < NW; ++w) u = fmin(u, s_red[w]);
-    s_U = u;
-  }
-  __syncthreads();
-  const double U = s_U;
-  const int cap = LEVEL == 0 ? kCoarseCap : kCap;
-
-  for (long long base = 0; base < n_src; base += blockDim.x) {
-    const long long i = base + tid;
-    bool keep = false;
-    long long s = 0;
-    if (i < n_src) {
-      s = src ? src[i] : i;
-      double LB, UB;
-      seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, img, amb);
-      const double slack = 1e-10 * (fabs(U) + fabs(LB) + 1.0);
-      keep = (LB - slack <= U + slack);  // never drops a seed that could tie or win
-    }
-    const unsigned bal = __ballot_sync(0xffffffffu, keep);
-    if (lane == 0) s_warp[warp] = __popc(bal);
-    __syncthreads();
-    int before = s_total;
-    for (int w = 0; w < warp; ++w) before += s_warp[w];
-    if (keep) {
-      const int slot = before + __popc(bal & ((1u << lane) - 1u));
-      if (slot < cap) {
-        if (LEVEL == 0) {
-          clist[(long long)tile * kCoarseCap + slot] = (int)s;
-        } else {
-          SeedRec r;
-          double p[3] = {seeds[s * ND], seeds[s * ND + 1], ND == 3 ? seeds[s * ND + 2] : 0.0};
-          if (g.periodic && g.mode == 0) {
-            if (amb) s_flag = 1;  // benign race: every writer stores 1
+__device__ __forceinline__ double warp_min(double v) {
 #pragma unroll
-            for (int a = 0; a < ND; ++a)  // fl(p + m L): the image coordinate the reference evaluates
-              p[a] = img[a] < 0 ? __dsub_rn(p[a], g.box[a]) : (img[a] > 0 ? __dadd_rn(p[a], g.box[a]) : p[a]);
-          }
-          r.x = p[0]; r.y = p[1]; r.z = p[2];
+  for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(kFull, v, o));
+  return v;
+}
+
+// ------------------------------------------------------------------------------------------
+// Coarse level: one CTA per coarse tile scans ALL seeds.  Seeds are taken interleaved (thread t,
+// round k -> seed 4096 c + 256 k + t: coalesced loads); the keep flags of a 4096-seed chunk go to a
+// shared bitmap whose prefix popcount gives every kept seed its slot, so the output is in
+// ascending seed index without a barrier per round.
+// ------------------------------------------------------------------------------------------
+template <int ND>
+__global__ void __launch_bounds__(256)
+coarse_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
+              int* __restrict__ clist, int* __restrict__ ccount) {
+  constexpr int kRounds = 16, kChunk = 256 * kRounds;
+  const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int t[3];
+  tile_coords(g.nc, tile, t);
+  double lo[3], hi[3];
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    lo[a] = (double)(t[a] * g.C[a]);
+    hi[a] = (double)(min(t[a] * g.C[a] + g.C[a], g.N[a]) - 1);
+  }
+  __shared__ double s_red[8];
+  __shared__ unsigned s_bits[kRounds * 8];
+  __shared__ int s_pref[kRounds * 8 + 1];
+  const long long n = g.S;
+  const bool cache = n <= kChunk;
+  double lbc[kRounds];
+  double best = INFINITY, pr[3];
+  bool amb;
+  for (long long c0 = 0; c0 < n; c0 += kChunk) {
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      const long long s = c0 + k * 256 + tid;
+      double LB = INFINITY, UB = INFINITY;
+      if (s < n) seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);
+      best = fmin(best, UB);
+      if (cache) lbc[k] = LB;
+    }
+  }
+  best = warp_min(best);
+  if (lane == 0) s_red[warp] = best;
+  __syncthreads();
+  double U = s_red[0];
+#pragma unroll
+  for (int w = 1; w < 8; ++w) U = fmin(U, s_red[w]);
+
+  int base = 0;
+  for (long long c0 = 0; c0 < n; c0 += kChunk) {
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      const long long s = c0 + k * 256 + tid;
+      double LB = INFINITY, UB;
+      if (cache) LB = lbc[k];
+      else if (s < n) seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);
+      const unsigned bal = __ballot_sync(kFull, s < n && may_win(LB, U));
+      if (lane == 0) s_bits[k * 8 + warp] = bal;
+    }
+    __syncthreads();
+    if (warp == 0) {  // exclusive prefix popcount over the 128 bitmap words
+      int v[4], sum = 0;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { v[j] = __popc(s_bits[lane * 4 + j]); sum += v[j]; }
+      int inc = sum;
+#pragma unroll
+      for (int o = 1; o < 32; o <<= 1) {
+        const int up = __shfl_up_sync(kFull, inc, o);
+        if (lane >= o) inc += up;
+      }
+      int run = inc - sum;
+#pragma unroll
+      for (int j = 0; j < 4; ++j) { s_pref[lane * 4 + j] = run; run += v[j]; }
+      if (lane == 31) s_pref[kRounds * 8] = inc;
+    }
+    __syncthreads();
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      const unsigned word = s_bits[k * 8 + warp];
+      if (word >> lane & 1u) {
+        const int slot = base + s_pref[k * 8 + warp] + __popc(word & ((1u << lane) - 1u));
+        if (slot < kCoarseCap) clist[(long long)tile * kCoarseCap + slot] = (int)(c0 + k * 256 + tid);
+      }
+    }
+    base += s_pref[kRounds * 8];
+    __syncthreads();
+  }
+  if (tid == 0) ccount[tile] = base;
+}
+
+// ------------------------------------------------------------------------------------------
+// Mid level: one warp per mid tile filters its parent's list (all seeds if the parent overflowed)
+// and writes staged records + indices in ascending seed index.  rcount = count | generic flag.
+// ------------------------------------------------------------------------------------------
+template <int ND>
+__global__ void __launch_bounds__(128)
+mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* __restrict__ weights,
+           const int* __restrict__ clist, const int* __restrict__ ccount, SeedRec* __restrict__ rec,
+           int* __restrict__ ridx, int* __restrict__ rcount) {
+  constexpr int kRounds = 8;
+  const int lane = threadIdx.x & 31;
+  const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+  if (tile >= n_mid) return;
+  int t[3];
+  tile_coords(g.nm, tile, t);
+  double lo[3], hi[3];
+  int parent = 0;
+#pragma unroll
+  for (int a = 0; a < 3; ++a) {
+    lo[a] = (double)(t[a] * g.M[a]);
+    hi[a] = (double)(min(t[a] * g.M[a] + g.M[a], g.N[a]) - 1);
+    parent = parent * g.nc[a] + (t[a] * g.M[a]) / g.C[a];
+  }
+  const int pc = ccount[parent];
+  const int* src = pc <= kCoarseCap ? clist + (long long)parent * kCoarseCap : nullptr;
+  const long long n = src ? pc : g.S;
+  const bool cache = n <= 32 * kRounds;
+  double lbc[kRounds];
+  double best = INFINITY, pr[3];
+  bool amb;
+  for (long long c0 = 0; c0 < n; c0 += 32 * kRounds) {
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      const long long i = c0 + k * 32 + lane;
+      double LB = INFINITY, UB = INFINITY;
+      if (i < n) seed_bounds<ND>(g, seeds, weights, src ? src[i] : i, lo, hi, LB, UB, pr, amb);
+      best = fmin(best, UB);
+      if (cache) lbc[k] = LB;
+    }
+  }
+  const double U = warp_min(best);
+  int base = 0;
+  bool any_amb = false;
+  for (long long c0 = 0; c0 < n; c0 += 32 * kRounds) {
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      const long long i = c0 + k * 32 + lane;
+      if (c0 + k * 32 >= n) break;
+      const long long s = i < n ? (src ? src[i] : i) : 0;
+      double LB = INFINITY, UB;
+      if (cache) LB = lbc[k];
+      else if (i < n) seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);
+      const bool keep = i < n && may_win(LB, U);
+      const unsigned bal = __ballot_sync(kFull, keep);
+      if (keep) {
+        const int slot = base + __popc(bal & ((1u << lane) - 1u));
+        seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);  // image-resolved coordinates
+        any_amb |= amb;
+        if (slot < kCap) {
+          SeedRec r;
+          r.x = pr[0]; r.y = pr[1]; r.z = pr[2];
           r.w = weights ? weights[s] : 0.0;
           rec[(long long)tile * kCap + slot] = r;
           ridx[(long long)tile * kCap + slot] = (int)s;
         }
       }
+      base += __popc(bal);
     }
-    __syncthreads();
-    if (tid == 0) {
-      int add = 0;
-      for (int w = 0; w < NW; ++w) add += s_warp[w];
-      s_total += add;
-    }
-    __syncthreads();
   }
-  if (tid == 0) {
-    if (LEVEL == 0) ccount[tile] = s_total;
-    else rcount[tile] = s_total | ((s_flag || g.mode == 1) ? kFlagGeneric : 0);
-  }
+  const bool generic = __any_sync(kFull, any_amb) || g.mode == 1;
+  if (lane == 0) rcount[tile] = base | (generic ? kFlagGeneric : 0);
 }
 
 // the reference expression for one seed at one voxel, all three images (voronoi.py:245 / :250-254)
 template <int ND>
-__device__ __forceinline__ double seed_value(const VorGeo& g, const double p[3], double w, double shift,
+__device__ __forceinline__ double seed_value(const VorGeo& g, const double* __restrict__ seeds, long long s, double w,
                                              const double x[3]) {
   double ss = 0.0;
+  const double shift = (double)s;
 #pragma unroll
-  for (int a = 0; a < ND; ++a) {
-    double d = __dsub_rn(p[a], x[a]);
+  for (int a = 3 - ND; a < 3; ++a) {
+    const double p = seed_coord<ND>(seeds, s, a);
+    double d = __dsub_rn(p, x[a]);
     if (g.mode == 1) d = __dadd_rn(d, shift);
     if (g.periodic) {
-      double dm = __dsub_rn(__dsub_rn(p[a], g.box[a]), x[a]);
-      double dp = __dsub_rn(__dadd_rn(p[a], g.box[a]), x[a]);
+      double dm = __dsub_rn(__dsub_rn(p, g.box[a]), x[a]);
+      double dp = __dsub_rn(__dadd_rn(p, g.box[a]), x[a]);
       if (g.mode == 1) { dm = __dadd_rn(dm, shift); dp = __dadd_rn(dp, shift); }
       d = fmin(fabs(d), fmin(fabs(dm), fabs(dp)));
     }
     const double sq = __dmul_rn(d, d);
-    ss = a == 0 ? sq : __dadd_rn(ss, sq);  // np.linalg.norm: sequential sum x -> y -> z
+    ss = a == 3 - ND ? sq : __dadd_rn(ss, sq);  // np.linalg.norm: sequential sum x -> y -> z
   }
   const double r = __dsqrt_rn(ss);
   return __dsub_rn(g.mode == 1 ? __dmul_rn(r, r) : r, w);
 }
 
-// sum of squares of (p - x), same operation order as the reference, image already resolved
-template <int ND>
-__device__ __forceinline__ double sumsq(const SeedRec& r, const double x[3]) {
-  const double dx = __dsub_rn(r.x, x[0]), dy = __dsub_rn(r.y, x[1]);
-  double ss = __dadd_rn(__dmul_rn(dx, dx), __dmul_rn(dy, dy));
-  if (ND == 3) {
-    const double dz = __dsub_rn(r.z, x[2]);
-    ss = __dadd_rn(ss, __dmul_rn(dz, dz));
-  }
-  return ss;
-}
+// Warp / lane geometry of the label kernel.  3D: mid tile 16^3 = 4 x 2 x 2 warps of 4 x 8 x 8 voxels;
+// 2D (1 x X x Y): mid tile 64 x 64 = 2 x 8 warps of 32 x 8 pixels.  A lane owns one column of 8.
+template <int ND> struct WarpTile;
+template <> struct WarpTile<3> {
+  static constexpr int M0 = 16, M1 = 16, M2 = 16, W0 = 4, W1 = 8;
+  __device__ static void origin(int warp, int o[3]) { o[0] = (warp & 3) * 4; o[1] = ((warp >> 2) & 1) * 8; o[2] = (warp >> 3) * 8; }
+  __device__ static void lane_xy(int lane, int& lx, int& ly) { lx = lane >> 3; ly = lane & 7; }
+};
+template <> struct WarpTile<2> {
+  static constexpr int M0 = 1, M1 = 64, M2 = 64, W0 = 1, W1 = 32;
+  __device__ static void origin(int warp, int o[3]) { o[0] = 0; o[1] = (warp & 1) * 32; o[2] = (warp >> 1) * 8; }
+  __device__ static void lane_xy(int lane, int& lx, int& ly) { lx = 0; ly = lane; }
+};
 
-// MODE 0: generic evaluation only (power mode).  MODE 1: additive, no weights -- compare sums of
-// squares and take the square root only inside a 2^-50 relative window, where rounding of the
-// root could turn "smaller" into "equal" (then the lower index keeps the voxel, like argmin).
-// MODE 2: additive with weights -- sqrt(ss) - w per candidate.
+// MODE 0: generic evaluation only (power mode).  MODE 1: additive, no weights -- bisector pruning,
+// compare sums of squares and take the square root only inside a 2^-50 relative window, where
+// rounding of the root could turn "smaller" into "equal" (then the lower index keeps the voxel, like
+// argmin).  MODE 2: additive with weights -- interval pruning, sqrt(ss) - w per candidate.
 template <int ND, int MODE>
-__global__ void __launch_bounds__(kTileVox)
-label_tiles_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
-                   const SeedRec* __restrict__ rec, const int* __restrict__ ridx,
-                   const int* __restrict__ rcount, const uint8_t* __restrict__ mask,
-                   int32_t* __restrict__ labels, unsigned long long* __restrict__ stats) {
+__global__ void __launch_bounds__(512, 2)
+label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
+             const SeedRec* __restrict__ rec, const int* __restrict__ ridx, const int* __restrict__ rcount,
+             const int* __restrict__ clist, const int* __restrict__ ccount, const uint8_t* __restrict__ mask,
+             int32_t* __restrict__ labels, unsigned long long* __restrict__ stats) {
+  using WT = WarpTile<ND>;
   __shared__ alignas(128) SeedRec s_rec[kCap];
   __shared__ alignas(16) int s_idx[kCap];
   __shared__ alignas(8) uint64_t s_bar;
-  const int tile = blockIdx.x, tid = threadIdx.x;
+  const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int raw = rcount[tile];
   const int count = raw & (kFlagGeneric - 1);
   const bool generic = MODE == 0 || (raw & kFlagGeneric) != 0;
@@ -299,71 +376,205 @@ label_tiles_kernel(VorGeo g, const double* __restrict__ seeds, const double* __r
     tma_bulk_g2s(s_idx, ridx + (long long)tile * kCap, b_idx, &s_bar);
   }
 
-  int t[3] = {0, 0, 0}, v[3] = {0, 0, 0};
-  tile_coords(g.nt, ND, tile, t);
-  {
-    int r = tid;
-    for (int a = ND - 1; a >= 0; --a) {
-      v[a] = t[a] * g.T[a] + r % g.T[a];
-      r /= g.T[a];
-    }
-  }
-  bool inside = true;
-  long long lin = 0;
-  for (int a = 0; a < ND; ++a) {
-    inside = inside && v[a] < g.N[a];
-    lin = lin * g.N[a] + v[a];
-  }
-  const bool live = inside && (!mask || mask[lin] != 0);
-  const double x[3] = {(double)v[0], (double)v[1], (double)v[2]};
-
-  if (staged) mbar_wait(&s_bar, 0);
-  int best_idx = -1;
-  if (live) {
-    if (!staged) {  // more possible winners than the staging buffer holds: scan every seed
-      double best = INFINITY;
-      for (long long s = 0; s < g.S; ++s) {
-        const double p[3] = {seeds[s * ND], seeds[s * ND + 1], ND == 3 ? seeds[s * ND + 2] : 0.0};
-        const double val = seed_value<ND>(g, p, weights ? weights[s] : 0.0, (double)s, x);
-        if (val < best || best_idx < 0) { best = val; best_idx = (int)s; }
-      }
-    } else if (generic) {  // records hold the original coordinates: evaluate all three images
-      double best = INFINITY;
-      for (int c = 0; c < count; ++c) {
-        const int si = s_idx[c];
-        const double p[3] = {seeds[(long long)si * ND], seeds[(long long)si * ND + 1], ND == 3 ? seeds[(long long)si * ND + 2] : 0.0};
-        const double val = seed_value<ND>(g, p, s_rec[c].w, (double)si, x);
-        if (val < best || best_idx < 0) { best = val; best_idx = si; }
-      }
-    } else if (MODE == 1) {
-      double best_ss = INFINITY, best_lo = INFINITY;
-#pragma unroll 2
-      for (int c = 0; c < count; ++c) {
-        const double ss = sumsq<ND>(s_rec[c], x);
-        bool take = ss < best_lo;
-        if (!take && ss < best_ss) take = __dsqrt_rn(ss) < __dsqrt_rn(best_ss);  // rare: roots may round together
-        if (take || best_idx < 0) {
-          best_ss = ss;
-          best_lo = __dmul_rn(ss, 1.0 - 0x1p-50);
-          best_idx = s_idx[c];
-        }
+  int t[3], o[3], lx, ly;
+  tile_coords(g.nm, tile, t);
+  WT::origin(warp, o);
+  WT::lane_xy(lane, lx, ly);
+  const int x0 = t[0] * WT::M0 + o[0], y0 = t[1] * WT::M1 + o[1], z0 = t[2] * WT::M2 + o[2];
+  if (x0 >= g.N[0] || y0 >= g.N[1] || z0 >= g.N[2]) return;  // whole warp outside the grid (no CTA barrier follows)
+  const int vx = x0 + lx, vy = y0 + ly;
+  const bool col_in = vx < g.N[0] && vy < g.N[1];
+  const int nz = min(kCol, g.N[2] - z0);
+  const long long lin = ((long long)vx * g.N[1] + vy) * g.N[2] + z0;
+  unsigned live = col_in ? (1u << nz) - 1u : 0u;
+  if (mask && col_in) {
+    if (nz == kCol && (reinterpret_cast<uintptr_t>(mask + lin) & 7) == 0) {
+      const uint2 mm = *reinterpret_cast<const uint2*>(mask + lin);
+      live = 0;
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        if ((mm.x >> (8 * k)) & 0xffu) live |= 1u << k;
+        if ((mm.y >> (8 * k)) & 0xffu) live |= 1u << (k + 4);
       }
     } else {
-      double best = INFINITY;
-#pragma unroll 2
-      for (int c = 0; c < count; ++c) {
-        const SeedRec r = s_rec[c];
-        const double val = __dsub_rn(__dsqrt_rn(sumsq<ND>(r, x)), r.w);
-        if (val < best || best_idx < 0) { best = val; best_idx = s_idx[c]; }
-      }
+      live = 0;
+      for (int k = 0; k < nz; ++k)
+        if (mask[lin + k]) live |= 1u << k;
     }
   }
-  if (inside) labels[lin] = best_idx;
+  const bool any_live = __any_sync(kFull, live != 0);
+  int bi[kCol];
+#pragma unroll
+  for (int k = 0; k < kCol; ++k) bi[k] = -1;
+  unsigned long long evals = 0;
+
+  if (staged) mbar_wait(&s_bar, 0);
+  if (any_live) {
+    if (!staged || generic) {
+      // generic path: every thread scans the candidate set with the three-image expression
+      const int* src = nullptr;
+      long long n = g.S;
+      if (staged) n = count;
+      else {
+        int parent = 0;
+#pragma unroll
+        for (int a = 0; a < 3; ++a) parent = parent * g.nc[a] + (t[a] * g.M[a]) / g.C[a];
+        const int pc = ccount[parent];
+        if (pc <= kCoarseCap) { src = clist + (long long)parent * kCoarseCap; n = pc; }
+      }
+      for (int k = 0; k < nz; ++k) {
+        if (!(live >> k & 1u)) continue;
+        const double x[3] = {(double)vx, (double)vy, (double)(z0 + k)};
+        double best = INFINITY;
+        int b = -1;
+        for (long long c = 0; c < n; ++c) {
+          const long long s = staged ? s_idx[c] : (src ? src[c] : c);
+          const double val = seed_value<ND>(g, seeds, s, weights ? weights[s] : 0.0, x);
+          if (val < best || b < 0) { best = val; b = (int)s; }
+        }
+        bi[k] = b;
+        evals += (unsigned long long)n;
+      }
+    } else {
+      // ---- warp-level pruning of the staged list; survivors = bits of m[] (ascending seed index)
+      const double lo[3] = {(double)x0, (double)y0, (double)z0};
+      const double hi[3] = {(double)(min(x0 + WT::W0, g.N[0]) - 1), (double)(min(y0 + WT::W1, g.N[1]) - 1),
+                            (double)(z0 + nz - 1)};
+      constexpr int kR = kCap / 32;
+      unsigned m[kR];
+      if (MODE == 1) {
+        // reference seed A: nearest to the sub-tile centre
+        const double cx = 0.5 * (lo[0] + hi[0]), cy = 0.5 * (lo[1] + hi[1]), cz = 0.5 * (lo[2] + hi[2]);
+        double bd = INFINITY;
+        int bc = 0;
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+          const int c = 32 * r + lane;
+          if (c < count) {
+            const SeedRec R = s_rec[c];
+            const double dx = R.x - cx, dy = R.y - cy, dz = R.z - cz;
+            const double d2 = (ND == 3 ? dx * dx : 0.0) + dy * dy + dz * dz;
+            if (d2 < bd) { bd = d2; bc = c; }
+          }
+        }
+#pragma unroll
+        for (int off = 16; off > 0; off >>= 1) {
+          const double od = __shfl_xor_sync(kFull, bd, off);
+          const int oc = __shfl_xor_sync(kFull, bc, off);
+          if (od < bd || (od == bd && oc < bc)) { bd = od; bc = oc; }
+        }
+        const SeedRec A = s_rec[bc];
+        const double ax0 = A.x - lo[0], ax1 = A.x - hi[0], ay0 = A.y - lo[1], ay1 = A.y - hi[1], az0 = A.z - lo[2], az1 = A.z - hi[2];
+        const double UA = (ND == 3 ? fmax(ax0 * ax0, ax1 * ax1) : 0.0) + fmax(ay0 * ay0, ay1 * ay1) + fmax(az0 * az0, az1 * az1);
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+          const int c = 32 * r + lane;
+          bool keep = false;
+          if (c < count) {
+            const SeedRec B = s_rec[c];
+            // min over the box of d_B^2 - d_A^2 = sum_a e_a (s_a - 2 x_a),  e = B - A,  s = B + A
+            double gmin = 0.0, scale = 0.0;
+            if (ND == 3) {
+              const double e = B.x - A.x, s = B.x + A.x;
+              gmin += fmin(e * (s - 2.0 * lo[0]), e * (s - 2.0 * hi[0]));
+              scale += fabs(e) * (fabs(A.x) + fabs(B.x) + 2.0 * hi[0] + 1.0);
+            }
+            {
+              const double e = B.y - A.y, s = B.y + A.y;
+              gmin += fmin(e * (s - 2.0 * lo[1]), e * (s - 2.0 * hi[1]));
+              scale += fabs(e) * (fabs(A.y) + fabs(B.y) + 2.0 * hi[1] + 1.0);
+            }
+            {
+              const double e = B.z - A.z, s = B.z + A.z;
+              gmin += fmin(e * (s - 2.0 * lo[2]), e * (s - 2.0 * hi[2]));
+              scale += fabs(e) * (fabs(A.z) + fabs(B.z) + 2.0 * hi[2] + 1.0);
+            }
+            keep = !(gmin > 1e-11 * (scale + UA + 1.0));  // B beats or ties A somewhere in the box (or NaN)
+          }
+          m[r] = __ballot_sync(kFull, keep);
+        }
+      } else {
+        double lb[kR], ub = INFINITY;
+#pragma unroll
+        for (int r = 0; r < kR; ++r) {
+          const int c = 32 * r + lane;
+          lb[r] = INFINITY;
+          if (c < count) {
+            const SeedRec R = s_rec[c];
+            double smin = 0.0, smax = 0.0;
+            const double q[3] = {R.x, R.y, R.z};
+#pragma unroll
+            for (int a = 3 - ND; a < 3; ++a) {
+              const double u = lo[a] - q[a], v = q[a] - hi[a];
+              const double dmin = fmax(0.0, fmax(u, v)), dmax = fmax(-u, -v);
+              smin += dmin * dmin;
+              smax += dmax * dmax;
+            }
+            lb[r] = sqrt(smin) - R.w;
+            ub = fmin(ub, sqrt(smax) - R.w);
+          }
+        }
+        const double U = warp_min(ub);
+#pragma unroll
+        for (int r = 0; r < kR; ++r) m[r] = __ballot_sync(kFull, 32 * r + lane < count && may_win(lb[r], U));
+      }
+
+      // ---- evaluation: column of kCol voxels per thread
+      const double X = (double)vx, Y = (double)vy;
+      double bs[kCol];
+#pragma unroll
+      for (int k = 0; k < kCol; ++k) bs[k] = INFINITY;
+      int kept = 0;
+#pragma unroll
+      for (int r = 0; r < kR; ++r) {
+        unsigned mm = m[r];
+        kept += __popc(mm);
+        while (mm) {
+          const int c = 32 * r + __ffs(mm) - 1;
+          mm &= mm - 1;
+          const SeedRec R = s_rec[c];
+          const int idx = s_idx[c];
+          const double dy = __dsub_rn(R.y, Y);
+          double sxy = __dmul_rn(dy, dy);
+          if (ND == 3) {
+            const double dx = __dsub_rn(R.x, X);
+            sxy = __dadd_rn(__dmul_rn(dx, dx), sxy);
+          }
+#pragma unroll
+          for (int k = 0; k < kCol; ++k) {
+            const double dz = __dsub_rn(R.z, (double)(z0 + k));
+            const double ss = __dadd_rn(sxy, __dmul_rn(dz, dz));
+            if (MODE == 1) {
+              if (ss < bs[k]) {
+                // roots of two sums closer than 2^-50 relative may round together: then the earlier index stays
+                if (ss < __dmul_rn(bs[k], 1.0 - 0x1p-50) || __dsqrt_rn(ss) < __dsqrt_rn(bs[k])) { bs[k] = ss; bi[k] = idx; }
+              }
+            } else {
+              const double val = __dsub_rn(__dsqrt_rn(ss), R.w);
+              if (val < bs[k] || bi[k] < 0) { bs[k] = val; bi[k] = idx; }
+            }
+          }
+        }
+      }
+      evals = (unsigned long long)kept * (unsigned long long)__popc(live);
+    }
+  }
+  if (col_in) {
+    if (nz == kCol && (reinterpret_cast<uintptr_t>(labels + lin) & 15) == 0) {
+      int4 a, b;
+      a.x = live & 1u ? bi[0] : -1; a.y = live & 2u ? bi[1] : -1; a.z = live & 4u ? bi[2] : -1; a.w = live & 8u ? bi[3] : -1;
+      b.x = live & 16u ? bi[4] : -1; b.y = live & 32u ? bi[5] : -1; b.z = live & 64u ? bi[6] : -1; b.w = live & 128u ? bi[7] : -1;
+      int4* dst = reinterpret_cast<int4*>(labels + lin);
+      dst[0] = a;
+      dst[1] = b;
+    } else {
+      for (int k = 0; k < nz; ++k) labels[lin + k] = (live >> k & 1u) ? bi[k] : -1;
+    }
+  }
   if (stats) {
-    const unsigned long long evals = live ? (unsigned long long)(staged ? count : g.S) : 0ull;
-    unsigned long long tot = evals;
-    for (int o = 16; o > 0; o >>= 1) tot += __shfl_xor_sync(0xffffffffu, tot, o);
-    if ((tid & 31) == 0 && tot) atomicAdd(&stats[0], tot);
+#pragma unroll
+    for (int off = 16; off > 0; off >>= 1) evals += __shfl_xor_sync(kFull, evals, off);
+    if (lane == 0 && evals) atomicAdd(&stats[0], evals);
     if (tid == 0) {
       atomicAdd(&stats[1], 1ull);
       if (!staged) atomicAdd(&stats[2], 1ull);
@@ -379,14 +590,14 @@ template <int ND>
 static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, const double* seeds, const double* weights,
                            int* clist, int* ccount, SeedRec* rec, int* ridx, int* rcount, const uint8_t* mask,
                            int32_t* labels, unsigned long long* stats, cudaStream_t st) {
-  candidates_kernel<ND, 0><<<(unsigned)ctiles, 256, 0, st>>>(g, seeds, weights, clist, ccount, nullptr, nullptr, nullptr);
-  candidates_kernel<ND, 1><<<(unsigned)tiles, 128, 0, st>>>(g, seeds, weights, clist, ccount, rec, ridx, rcount);
+  coarse_kernel<ND><<<(unsigned)ctiles, 256, 0, st>>>(g, seeds, weights, clist, ccount);
+  mid_kernel<ND><<<(unsigned)((tiles + 3) / 4), 128, 0, st>>>(g, (int)tiles, seeds, weights, clist, ccount, rec, ridx, rcount);
   if (g.mode == 1)
-    label_tiles_kernel<ND, 0><<<(unsigned)tiles, kTileVox, 0, st>>>(g, seeds, weights, rec, ridx, rcount, mask, labels, stats);
+    label_kernel<ND, 0><<<(unsigned)tiles, 512, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
   else if (!weights)
-    label_tiles_kernel<ND, 1><<<(unsigned)tiles, kTileVox, 0, st>>>(g, seeds, weights, rec, ridx, rcount, mask, labels, stats);
+    label_kernel<ND, 1><<<(unsigned)tiles, 512, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
   else
-    label_tiles_kernel<ND, 2><<<(unsigned)tiles, kTileVox, 0, st>>>(g, seeds, weights, rec, ridx, rcount, mask, labels, stats);
+    label_kernel<ND, 2><<<(unsigned)tiles, 512, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
 }
 
 extern "C" int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
@@ -402,29 +613,35 @@ extern "C" int sbx_voronoi_label(int device, int ndim, const int64_t* N, const d
   cudaStream_t st = (cudaStream_t)stream;
 
   VorGeo g{};
-  g.ndim = ndim;
+  g.nd = ndim;
   g.mode = mode;
   g.S = S;
   g.periodic = box_host ? 1 : 0;
-  const int tile3[3] = {8, 8, 8}, tile2[3] = {16, 32, 1};
+  const int mid3[3] = {16, 16, 16}, mid2[3] = {1, 64, 64};
+  const int coarse3[3] = {32, 32, 32}, coarse2[3] = {1, 256, 256};
   long long tiles = 1, ctiles = 1;
+  const int off = 3 - ndim;  // internal axis of real axis 0
   for (int a = 0; a < 3; ++a) {
-    g.N[a] = 1; g.T[a] = 1; g.nt[a] = 1; g.ct[a] = 1; g.box[a] = 0.0;
+    g.N[a] = 1;
+    g.box[a] = 1.0;
+    g.M[a] = ndim == 3 ? mid3[a] : mid2[a];
+    g.C[a] = ndim == 3 ? coarse3[a] : coarse2[a];
   }
   for (int a = 0; a < ndim; ++a) {
     if (N[a] < 1 || N[a] > (1 << 20)) return fail(SBX_EINVAL, "N[%d]=%lld out of range", a, (long long)N[a]);
-    g.N[a] = (int)N[a];
-    g.T[a] = ndim == 3 ? tile3[a] : tile2[a];
-    g.nt[a] = (g.N[a] + g.T[a] - 1) / g.T[a];
-    g.ct[a] = (g.nt[a] + kCF - 1) / kCF;
-    tiles *= g.nt[a];
-    ctiles *= g.ct[a];
+    g.N[a + off] = (int)N[a];
     if (box_host) {
       if (!(box_host[a] > 0.0)) return fail(SBX_EINVAL, "box[%d] must be > 0", a);
-      g.box[a] = box_host[a];
+      g.box[a + off] = box_host[a];
     }
   }
-  if (tiles > 0x7fffffff) return fail(SBX_EINVAL, "grid too large (%lld tiles)", tiles);
+  for (int a = 0; a < 3; ++a) {
+    g.nm[a] = (g.N[a] + g.M[a] - 1) / g.M[a];
+    g.nc[a] = (g.N[a] + g.C[a] - 1) / g.C[a];
+    tiles *= g.nm[a];
+    ctiles *= g.nc[a];
+  }
+  if (tiles > 0x3fffffff) return fail(SBX_EINVAL, "grid too large (%lld tiles)", tiles);
 
   SeedRec* rec = nullptr;
   int *ridx = nullptr, *rcount = nullptr, *clist = nullptr, *ccount = nullptr;
