@@ -401,7 +401,7 @@ def run_voronoi(args):
         "e2e": {"value": vox * grids * world / (e2e_ms * 1e-3), "unit": "voxels/s", "h2d_bytes_per_step": grids * (S * 24 + vox),
                 "d2h_bytes_per_step": grids * vox * 4, "ms_per_step": e2e_ms, "api": "VoronoiCell.label_grid(host seeds, host mask) -> host labels"},
         "gpu_launches": 3 * grids * args.steps,
-        "roofline": {"bound": "hbm", "kernel": "candidates_kernel<coarse>+candidates_kernel<fine>+label_tiles_kernel", "achieved": achieved, "peak": peak,
+        "roofline": {"bound": "hbm", "kernel": "coarse_kernel+mid_kernel+label_kernel", "achieved": achieved, "peak": peak,
                      "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_grid": unit_bytes, "evaluations_per_live_voxel": st["evaluations"] / max(live, 1),
                      "overflow_tiles": st["overflow_tiles"]},

@@ -8,12 +8,12 @@
 //      inside it, out of all S seeds (interval bounds with slack, ascending seed index);
 //   2. mid_kernel: one warp per MID tile (16^3 / 64^2) filters its parent's list and writes staged
 //      records: fl(p + m L) of the single periodic image that is nearest for the whole tile;
-//   3. label_kernel: one CTA per mid tile.  The records arrive in shared memory by TMA bulk copy
+//   3. label_kernel: one CTA per half mid tile.  The records arrive in shared memory by TMA bulk copy
 //      (cp.async.bulk + mbarrier).  Every warp owns a 4x8x8 (1x32x8) sub-tile, prunes the list once
 //      more -- for unweighted seeds with the exact bisector test (d_B^2 - d_A^2 is affine in x, so its
-//      minimum over a box sits on a corner) -- and keeps the survivors as ballot bit masks.  Every
+//      minimum over a box sits on a corner) -- and keeps the survivors in a per-warp list.  Every
 //      thread owns a column of 8 voxels along the last axis: (dx^2 + dy^2) is formed once per
-//      candidate and dz^2 added per voxel, in the reference's summation order, with round-to-nearest
+//      candidate and dz^2 (computed once per warp) added per voxel, in the reference's summation order, with round-to-nearest
 //      intrinsics (no FMA contraction).  First minimum wins (np.argmin).
 // Periodic boxes use the minimum image per axis, which equals the minimum over the 3^d replicated
 // images of the reference expression because every fp64 step is monotone.  Tiles where no single
@@ -60,53 +60,62 @@ __device__ __forceinline__ double seed_coord(const double* __restrict__ seeds, l
   return seeds[s * ND + (a - (3 - ND))];
 }
 
-// Conservative bounds of the seed's value over the voxel box [lo, hi] (internal axes, doubles).
-// pr[] receives the coordinate of the periodic image nearest to the box centre (fl(p +- L), the
-// number the reference evaluates); `amb` is set when some other image may be nearer for a voxel of
-// the box -- the bounds then cover all three images.
+// Conservative bounds of the seed's value over the voxel box with centre c and half extent h
+// (internal axes).  Periodic boxes use the allowed image (p, p - L or p + L) nearest to the centre:
+// for every voxel x of the box and every allowed image q', |q' - x| >= |q' - c| - h >= |q - c| - h,
+// and the true value is at most |q - x| <= |q - c| + h, so both bounds hold whichever image is
+// nearest to x.  `amb` is set when another image may be nearer for some voxel of the box (the
+// evaluation then has to look at all three images).  Keys: additive without weights compares
+// squared distances (no square root); additive with weights sqrt(.) - w; power (.) - w.
 template <int ND>
-__device__ __forceinline__ void seed_bounds(const VorGeo& g, const double* __restrict__ seeds,
-                                            const double* __restrict__ weights, long long s, const double lo[3],
-                                            const double hi[3], double& LB, double& UB, double pr[3], bool& amb) {
+__device__ __forceinline__ void tile_bounds(const VorGeo& g, const double* __restrict__ seeds,
+                                            const double* __restrict__ weights, long long s, const double c[3],
+                                            const double h[3], double& LB, double& UB, bool& amb) {
   double smin = 0.0, smax = 0.0;
   amb = false;
+#pragma unroll
+  for (int a = 3 - ND; a < 3; ++a) {
+    double p = seed_coord<ND>(seeds, s, a);
+    if (g.mode == 1) p += (double)s;  // voronoi.py:251 adds the seed index to every coordinate
+    double d = p - c[a];
+    if (g.periodic) {
+      const double L = g.box[a], hL = 0.5 * L;
+      if (d > hL) d -= L;
+      else if (d < -hL) d += L;
+      amb |= !(fabs(d) + h[a] < hL - 1e-9 * (L + 1.0));
+    }
+    const double t = fabs(d);
+    const double dmax = t + h[a], dmin = fmax(t - h[a], 0.0);
+    smin += dmin * dmin;
+    smax += dmax * dmax;
+  }
+  if (g.mode == 1) {
+    const double w = weights ? weights[s] : 0.0;
+    LB = smin - w; UB = smax - w;
+  } else if (weights) {
+    const double w = weights[s];
+    LB = sqrt(smin) - w; UB = sqrt(smax) - w;
+  } else {
+    LB = smin; UB = smax;
+  }
+}
+
+// fl(p + m L) of the image tile_bounds picked: the number the reference evaluates for that image
+template <int ND>
+__device__ __forceinline__ void resolve_image(const VorGeo& g, const double* __restrict__ seeds, long long s,
+                                              const double c[3], double pr[3]) {
   pr[0] = 0.0;
 #pragma unroll
   for (int a = 3 - ND; a < 3; ++a) {
     const double p0 = seed_coord<ND>(seeds, s, a);
-    double p = p0;
-    if (g.mode == 1) p += (double)s;  // voronoi.py:251 adds the seed index to every coordinate
-    double q = p;
-    const double L = g.box[a];
+    pr[a] = p0;
     if (g.periodic) {
-      const double d = p - 0.5 * (lo[a] + hi[a]);
-      if (d > 0.5 * L) { q = p - L; pr[a] = __dsub_rn(p0, L); }
-      else if (d < -0.5 * L) { q = p + L; pr[a] = __dadd_rn(p0, L); }
-      else pr[a] = p0;
-    } else {
-      pr[a] = p0;
+      const double d = (g.mode == 1 ? p0 + (double)s : p0) - c[a];
+      const double L = g.box[a], hL = 0.5 * L;
+      if (d > hL) pr[a] = __dsub_rn(p0, L);
+      else if (d < -hL) pr[a] = __dadd_rn(p0, L);
     }
-    const double u = lo[a] - q, v = q - hi[a];
-    double dmin = fmax(0.0, fmax(u, v));
-    double dmax = fmax(-u, -v);
-    if (g.periodic && !(dmax < 0.5 * L - 1e-9 * (L + 1.0))) {
-      amb = true;  // all three images of the reference: smallest lower bound, smallest upper bound
-      const double qs[3] = {p - L, p, p + L};
-      dmin = INFINITY;
-      dmax = INFINITY;
-#pragma unroll
-      for (int i = 0; i < 3; ++i) {
-        const double uu = lo[a] - qs[i], vv = qs[i] - hi[a];
-        dmin = fmin(dmin, fmax(0.0, fmax(uu, vv)));
-        dmax = fmin(dmax, fmax(-uu, -vv));
-      }
-    }
-    smin += dmin * dmin;
-    smax += dmax * dmax;
   }
-  const double w = weights ? weights[s] : 0.0;
-  if (g.mode == 0) { LB = sqrt(smin) - w; UB = sqrt(smax) - w; }
-  else { LB = smin - w; UB = smax - w; }
 }
 
 __device__ __forceinline__ bool may_win(double LB, double U) {
@@ -151,40 +160,42 @@ __device__ __forceinline__ double warp_min(double v) {
 
 // ------------------------------------------------------------------------------------------
 // Coarse level: one CTA per coarse tile scans ALL seeds.  Seeds are taken interleaved (thread t,
-// round k -> seed 4096 c + 256 k + t: coalesced loads); the keep flags of a 4096-seed chunk go to a
-// shared bitmap whose prefix popcount gives every kept seed its slot, so the output is in
-// ascending seed index without a barrier per round.
+// round k -> seed 4096 c + 256 k + t: coalesced loads); lower bounds of a 4096-seed chunk are
+// cached in shared memory, the keep flags go to a shared bitmap whose prefix popcount gives every
+// kept seed its slot, so the output is in ascending seed index without a barrier per round.
 // ------------------------------------------------------------------------------------------
 template <int ND>
-__global__ void __launch_bounds__(256)
+__global__ void __launch_bounds__(256, 4)
 coarse_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
               int* __restrict__ clist, int* __restrict__ ccount) {
   constexpr int kRounds = 16, kChunk = 256 * kRounds;
   const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int t[3];
   tile_coords(g.nc, tile, t);
-  double lo[3], hi[3];
+  double c[3], h[3];
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
-    lo[a] = (double)(t[a] * g.C[a]);
-    hi[a] = (double)(min(t[a] * g.C[a] + g.C[a], g.N[a]) - 1);
+    const double lo = (double)(t[a] * g.C[a]);
+    const double hi = (double)(min(t[a] * g.C[a] + g.C[a], g.N[a]) - 1);
+    c[a] = 0.5 * (lo + hi);
+    h[a] = 0.5 * (hi - lo);
   }
+  __shared__ double s_lb[kChunk];
   __shared__ double s_red[8];
   __shared__ unsigned s_bits[kRounds * 8];
   __shared__ int s_pref[kRounds * 8 + 1];
   const long long n = g.S;
   const bool cache = n <= kChunk;
-  double lbc[kRounds];
-  double best = INFINITY, pr[3];
+  double best = INFINITY;
   bool amb;
   for (long long c0 = 0; c0 < n; c0 += kChunk) {
-#pragma unroll
+#pragma unroll 2
     for (int k = 0; k < kRounds; ++k) {
       const long long s = c0 + k * 256 + tid;
       double LB = INFINITY, UB = INFINITY;
-      if (s < n) seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);
+      if (s < n) tile_bounds<ND>(g, seeds, weights, s, c, h, LB, UB, amb);
       best = fmin(best, UB);
-      if (cache) lbc[k] = LB;
+      if (cache) s_lb[k * 256 + tid] = LB;
     }
   }
   best = warp_min(best);
@@ -196,12 +207,12 @@ coarse_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restri
 
   int base = 0;
   for (long long c0 = 0; c0 < n; c0 += kChunk) {
-#pragma unroll
+#pragma unroll 2
     for (int k = 0; k < kRounds; ++k) {
       const long long s = c0 + k * 256 + tid;
       double LB = INFINITY, UB;
-      if (cache) LB = lbc[k];
-      else if (s < n) seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);
+      if (cache) LB = s_lb[k * 256 + tid];
+      else if (s < n) tile_bounds<ND>(g, seeds, weights, s, c, h, LB, UB, amb);
       const unsigned bal = __ballot_sync(kFull, s < n && may_win(LB, U));
       if (lane == 0) s_bits[k * 8 + warp] = bal;
     }
@@ -222,7 +233,7 @@ coarse_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restri
       if (lane == 31) s_pref[kRounds * 8] = inc;
     }
     __syncthreads();
-#pragma unroll
+#pragma unroll 4
     for (int k = 0; k < kRounds; ++k) {
       const unsigned word = s_bits[k * 8 + warp];
       if (word >> lane & 1u) {
@@ -241,60 +252,64 @@ coarse_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restri
 // and writes staged records + indices in ascending seed index.  rcount = count | generic flag.
 // ------------------------------------------------------------------------------------------
 template <int ND>
-__global__ void __launch_bounds__(128)
+__global__ void __launch_bounds__(128, 8)
 mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* __restrict__ weights,
            const int* __restrict__ clist, const int* __restrict__ ccount, SeedRec* __restrict__ rec,
            int* __restrict__ ridx, int* __restrict__ rcount) {
-  constexpr int kRounds = 8;
-  const int lane = threadIdx.x & 31;
-  const int tile = blockIdx.x * 4 + (threadIdx.x >> 5);
+  constexpr int kRounds = 8, kChunk = 32 * kRounds;
+  __shared__ double s_lb[4][kChunk];
+  const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+  const int tile = blockIdx.x * 4 + warp;
   if (tile >= n_mid) return;
   int t[3];
   tile_coords(g.nm, tile, t);
-  double lo[3], hi[3];
+  double c[3], h[3];
   int parent = 0;
 #pragma unroll
   for (int a = 0; a < 3; ++a) {
-    lo[a] = (double)(t[a] * g.M[a]);
-    hi[a] = (double)(min(t[a] * g.M[a] + g.M[a], g.N[a]) - 1);
+    const double lo = (double)(t[a] * g.M[a]);
+    const double hi = (double)(min(t[a] * g.M[a] + g.M[a], g.N[a]) - 1);
+    c[a] = 0.5 * (lo + hi);
+    h[a] = 0.5 * (hi - lo);
     parent = parent * g.nc[a] + (t[a] * g.M[a]) / g.C[a];
   }
   const int pc = ccount[parent];
   const int* src = pc <= kCoarseCap ? clist + (long long)parent * kCoarseCap : nullptr;
   const long long n = src ? pc : g.S;
-  const bool cache = n <= 32 * kRounds;
-  double lbc[kRounds];
-  double best = INFINITY, pr[3];
+  const bool cache = n <= kChunk;
+  double best = INFINITY;
   bool amb;
-  for (long long c0 = 0; c0 < n; c0 += 32 * kRounds) {
-#pragma unroll
+  for (long long c0 = 0; c0 < n; c0 += kChunk) {
+#pragma unroll 2
     for (int k = 0; k < kRounds; ++k) {
       const long long i = c0 + k * 32 + lane;
       double LB = INFINITY, UB = INFINITY;
-      if (i < n) seed_bounds<ND>(g, seeds, weights, src ? src[i] : i, lo, hi, LB, UB, pr, amb);
+      if (i < n) tile_bounds<ND>(g, seeds, weights, src ? src[i] : i, c, h, LB, UB, amb);
       best = fmin(best, UB);
-      if (cache) lbc[k] = LB;
+      if (cache) s_lb[warp][k * 32 + lane] = LB;
     }
   }
   const double U = warp_min(best);
   int base = 0;
   bool any_amb = false;
-  for (long long c0 = 0; c0 < n; c0 += 32 * kRounds) {
-#pragma unroll
+  for (long long c0 = 0; c0 < n; c0 += kChunk) {
+#pragma unroll 2
     for (int k = 0; k < kRounds; ++k) {
-      const long long i = c0 + k * 32 + lane;
       if (c0 + k * 32 >= n) break;
+      const long long i = c0 + k * 32 + lane;
       const long long s = i < n ? (src ? src[i] : i) : 0;
       double LB = INFINITY, UB;
-      if (cache) LB = lbc[k];
-      else if (i < n) seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);
+      if (cache) LB = s_lb[warp][k * 32 + lane];
+      else if (i < n) tile_bounds<ND>(g, seeds, weights, s, c, h, LB, UB, amb);
       const bool keep = i < n && may_win(LB, U);
       const unsigned bal = __ballot_sync(kFull, keep);
       if (keep) {
         const int slot = base + __popc(bal & ((1u << lane) - 1u));
-        seed_bounds<ND>(g, seeds, weights, s, lo, hi, LB, UB, pr, amb);  // image-resolved coordinates
+        tile_bounds<ND>(g, seeds, weights, s, c, h, LB, UB, amb);
         any_amb |= amb;
         if (slot < kCap) {
+          double pr[3];
+          resolve_image<ND>(g, seeds, s, c, pr);
           SeedRec r;
           r.x = pr[0]; r.y = pr[1]; r.z = pr[2];
           r.w = weights ? weights[s] : 0.0;
@@ -333,26 +348,28 @@ __device__ __forceinline__ double seed_value(const VorGeo& g, const double* __re
   return __dsub_rn(g.mode == 1 ? __dmul_rn(r, r) : r, w);
 }
 
-// Warp / lane geometry of the label kernel.  3D: mid tile 16^3 = 4 x 2 x 2 warps of 4 x 8 x 8 voxels;
-// 2D (1 x X x Y): mid tile 64 x 64 = 2 x 8 warps of 32 x 8 pixels.  A lane owns one column of 8.
+// Warp / lane geometry of the label kernel.  A CTA of 8 warps labels HALF a mid tile (split along the
+// last axis).  3D: mid tile 16^3, half = 16 x 16 x 8 = 4 x 2 warps of 4 x 8 x 8 voxels;
+// 2D (1 x X x Y): mid tile 64 x 64, half = 64 x 32 = 2 x 4 warps of 32 x 8 pixels.  A lane owns one
+// column of 8 voxels along the last axis.
 template <int ND> struct WarpTile;
 template <> struct WarpTile<3> {
   static constexpr int M0 = 16, M1 = 16, M2 = 16, W0 = 4, W1 = 8;
-  __device__ static void origin(int warp, int o[3]) { o[0] = (warp & 3) * 4; o[1] = ((warp >> 2) & 1) * 8; o[2] = (warp >> 3) * 8; }
+  __device__ static void origin(int warp, int half, int o[3]) { o[0] = (warp & 3) * 4; o[1] = (warp >> 2) * 8; o[2] = half * 8; }
   __device__ static void lane_xy(int lane, int& lx, int& ly) { lx = lane >> 3; ly = lane & 7; }
 };
 template <> struct WarpTile<2> {
   static constexpr int M0 = 1, M1 = 64, M2 = 64, W0 = 1, W1 = 32;
-  __device__ static void origin(int warp, int o[3]) { o[0] = 0; o[1] = (warp & 1) * 32; o[2] = (warp >> 1) * 8; }
+  __device__ static void origin(int warp, int half, int o[3]) { o[0] = 0; o[1] = (warp & 1) * 32; o[2] = half * 32 + (warp >> 1) * 8; }
   __device__ static void lane_xy(int lane, int& lx, int& ly) { lx = 0; ly = lane; }
 };
 
 // MODE 0: generic evaluation only (power mode).  MODE 1: additive, no weights -- bisector pruning,
-// compare sums of squares and take the square root only inside a 2^-50 relative window, where
+// compare sums of squares and take the square root only when the two sums are within 8 ulps, where
 // rounding of the root could turn "smaller" into "equal" (then the lower index keeps the voxel, like
 // argmin).  MODE 2: additive with weights -- interval pruning, sqrt(ss) - w per candidate.
 template <int ND, int MODE>
-__global__ void __launch_bounds__(512, 2)
+__global__ void __launch_bounds__(256, 3)
 label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
              const SeedRec* __restrict__ rec, const int* __restrict__ ridx, const int* __restrict__ rcount,
              const int* __restrict__ clist, const int* __restrict__ ccount, const uint8_t* __restrict__ mask,
@@ -360,8 +377,11 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
   using WT = WarpTile<ND>;
   __shared__ alignas(128) SeedRec s_rec[kCap];
   __shared__ alignas(16) int s_idx[kCap];
+  __shared__ alignas(16) double s_dz[8][32];      // per warp: (z_c - z_k)^2 of a batch of 4 candidates x 8 voxels
+  __shared__ unsigned char s_list[8][kCap];       // per warp: surviving record slots, ascending
   __shared__ alignas(8) uint64_t s_bar;
-  const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int tile = blockIdx.x >> 1, half = blockIdx.x & 1;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int raw = rcount[tile];
   const int count = raw & (kFlagGeneric - 1);
   const bool generic = MODE == 0 || (raw & kFlagGeneric) != 0;
@@ -378,7 +398,7 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
 
   int t[3], o[3], lx, ly;
   tile_coords(g.nm, tile, t);
-  WT::origin(warp, o);
+  WT::origin(warp, half, o);
   WT::lane_xy(lane, lx, ly);
   const int x0 = t[0] * WT::M0 + o[0], y0 = t[1] * WT::M1 + o[1], z0 = t[2] * WT::M2 + o[2];
   if (x0 >= g.N[0] || y0 >= g.N[1] || z0 >= g.N[2]) return;  // whole warp outside the grid (no CTA barrier follows)
@@ -427,8 +447,8 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
         const double x[3] = {(double)vx, (double)vy, (double)(z0 + k)};
         double best = INFINITY;
         int b = -1;
-        for (long long c = 0; c < n; ++c) {
-          const long long s = staged ? s_idx[c] : (src ? src[c] : c);
+        for (long long cidx = 0; cidx < n; ++cidx) {
+          const long long s = staged ? s_idx[cidx] : (src ? src[cidx] : cidx);
           const double val = seed_value<ND>(g, seeds, s, weights ? weights[s] : 0.0, x);
           if (val < best || b < 0) { best = val; b = (int)s; }
         }
@@ -436,19 +456,19 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
         evals += (unsigned long long)n;
       }
     } else {
-      // ---- warp-level pruning of the staged list; survivors = bits of m[] (ascending seed index)
+      // ---- warp-level pruning of the staged list; survivors -> s_list[warp] (ascending seed index)
       const double lo[3] = {(double)x0, (double)y0, (double)z0};
       const double hi[3] = {(double)(min(x0 + WT::W0, g.N[0]) - 1), (double)(min(y0 + WT::W1, g.N[1]) - 1),
                             (double)(z0 + nz - 1)};
       constexpr int kR = kCap / 32;
-      unsigned m[kR];
+      const int rounds = (count + 31) >> 5;
+      int kept = 0;
       if (MODE == 1) {
         // reference seed A: nearest to the sub-tile centre
         const double cx = 0.5 * (lo[0] + hi[0]), cy = 0.5 * (lo[1] + hi[1]), cz = 0.5 * (lo[2] + hi[2]);
         double bd = INFINITY;
         int bc = 0;
-#pragma unroll
-        for (int r = 0; r < kR; ++r) {
+        for (int r = 0; r < rounds; ++r) {
           const int c = 32 * r + lane;
           if (c < count) {
             const SeedRec R = s_rec[c];
@@ -466,8 +486,7 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
         const SeedRec A = s_rec[bc];
         const double ax0 = A.x - lo[0], ax1 = A.x - hi[0], ay0 = A.y - lo[1], ay1 = A.y - hi[1], az0 = A.z - lo[2], az1 = A.z - hi[2];
         const double UA = (ND == 3 ? fmax(ax0 * ax0, ax1 * ax1) : 0.0) + fmax(ay0 * ay0, ay1 * ay1) + fmax(az0 * az0, az1 * az1);
-#pragma unroll
-        for (int r = 0; r < kR; ++r) {
+        for (int r = 0; r < rounds; ++r) {
           const int c = 32 * r + lane;
           bool keep = false;
           if (c < count) {
@@ -491,7 +510,9 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
             }
             keep = !(gmin > 1e-11 * (scale + UA + 1.0));  // B beats or ties A somewhere in the box (or NaN)
           }
-          m[r] = __ballot_sync(kFull, keep);
+          const unsigned bal = __ballot_sync(kFull, keep);
+          if (keep) s_list[warp][kept + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)c;
+          kept += __popc(bal);
         }
       } else {
         double lb[kR], ub = INFINITY;
@@ -516,45 +537,64 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
         }
         const double U = warp_min(ub);
 #pragma unroll
-        for (int r = 0; r < kR; ++r) m[r] = __ballot_sync(kFull, 32 * r + lane < count && may_win(lb[r], U));
+        for (int r = 0; r < kR; ++r) {
+          const int c = 32 * r + lane;
+          const bool keep = c < count && may_win(lb[r], U);
+          const unsigned bal = __ballot_sync(kFull, keep);
+          if (keep) s_list[warp][kept + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)c;
+          kept += __popc(bal);
+        }
       }
+      __syncwarp();
 
-      // ---- evaluation: column of kCol voxels per thread
+      // ---- evaluation: column of kCol voxels per thread; (z_c - z_k)^2 shared by the warp, 4 candidates a batch
       const double X = (double)vx, Y = (double)vy;
       double bs[kCol];
 #pragma unroll
       for (int k = 0; k < kCol; ++k) bs[k] = INFINITY;
-      int kept = 0;
-#pragma unroll
-      for (int r = 0; r < kR; ++r) {
-        unsigned mm = m[r];
-        kept += __popc(mm);
-        while (mm) {
-          const int c = 32 * r + __ffs(mm) - 1;
-          mm &= mm - 1;
-          const SeedRec R = s_rec[c];
+      for (int b0 = 0; b0 < kept; b0 += 4) {
+        {
+          const int j = b0 + (lane >> 3);
+          if (j < kept) {
+            const double dz = __dsub_rn(s_rec[s_list[warp][j]].z, (double)(z0 + (lane & 7)));
+            s_dz[warp][lane] = __dmul_rn(dz, dz);
+          }
+        }
+        __syncwarp();
+        const int nb = min(4, kept - b0);
+        for (int j = 0; j < nb; ++j) {
+          const int c = s_list[warp][b0 + j];
+          const double2 Rxy = *reinterpret_cast<const double2*>(&s_rec[c]);
           const int idx = s_idx[c];
-          const double dy = __dsub_rn(R.y, Y);
+          const double dy = __dsub_rn(Rxy.y, Y);
           double sxy = __dmul_rn(dy, dy);
           if (ND == 3) {
-            const double dx = __dsub_rn(R.x, X);
+            const double dx = __dsub_rn(Rxy.x, X);
             sxy = __dadd_rn(__dmul_rn(dx, dx), sxy);
           }
+          double w = 0.0;
+          if (MODE == 2) w = s_rec[c].w;
+          const double2* dzp = reinterpret_cast<const double2*>(&s_dz[warp][8 * j]);
 #pragma unroll
-          for (int k = 0; k < kCol; ++k) {
-            const double dz = __dsub_rn(R.z, (double)(z0 + k));
-            const double ss = __dadd_rn(sxy, __dmul_rn(dz, dz));
-            if (MODE == 1) {
-              if (ss < bs[k]) {
-                // roots of two sums closer than 2^-50 relative may round together: then the earlier index stays
-                if (ss < __dmul_rn(bs[k], 1.0 - 0x1p-50) || __dsqrt_rn(ss) < __dsqrt_rn(bs[k])) { bs[k] = ss; bi[k] = idx; }
+          for (int k2 = 0; k2 < kCol / 2; ++k2) {
+            const double2 d2 = dzp[k2];
+#pragma unroll
+            for (int q = 0; q < 2; ++q) {
+              const int k = 2 * k2 + q;
+              const double ss = __dadd_rn(sxy, q ? d2.y : d2.x);
+              if (MODE == 1) {
+                bool take = ss < bs[k];
+                // sums within 8 ulps: their roots may round together, then the earlier index stays
+                if (take && __double_as_longlong(bs[k]) - __double_as_longlong(ss) <= 8) take = __dsqrt_rn(ss) < __dsqrt_rn(bs[k]);
+                if (take) { bs[k] = ss; bi[k] = idx; }
+              } else {
+                const double val = __dsub_rn(__dsqrt_rn(ss), w);
+                if (val < bs[k] || bi[k] < 0) { bs[k] = val; bi[k] = idx; }
               }
-            } else {
-              const double val = __dsub_rn(__dsqrt_rn(ss), R.w);
-              if (val < bs[k] || bi[k] < 0) { bs[k] = val; bi[k] = idx; }
             }
           }
         }
+        __syncwarp();
       }
       evals = (unsigned long long)kept * (unsigned long long)__popc(live);
     }
@@ -575,7 +615,7 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) evals += __shfl_xor_sync(kFull, evals, off);
     if (lane == 0 && evals) atomicAdd(&stats[0], evals);
-    if (tid == 0) {
+    if (tid == 0 && half == 0) {
       atomicAdd(&stats[1], 1ull);
       if (!staged) atomicAdd(&stats[2], 1ull);
     }
@@ -593,11 +633,11 @@ static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, c
   coarse_kernel<ND><<<(unsigned)ctiles, 256, 0, st>>>(g, seeds, weights, clist, ccount);
   mid_kernel<ND><<<(unsigned)((tiles + 3) / 4), 128, 0, st>>>(g, (int)tiles, seeds, weights, clist, ccount, rec, ridx, rcount);
   if (g.mode == 1)
-    label_kernel<ND, 0><<<(unsigned)tiles, 512, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+    label_kernel<ND, 0><<<(unsigned)tiles * 2, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
   else if (!weights)
-    label_kernel<ND, 1><<<(unsigned)tiles, 512, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+    label_kernel<ND, 1><<<(unsigned)tiles * 2, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
   else
-    label_kernel<ND, 2><<<(unsigned)tiles, 512, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+    label_kernel<ND, 2><<<(unsigned)tiles * 2, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
 }
 
 extern "C" int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
