@@ -130,10 +130,22 @@ int sbx_scatter_execute_host(sbx_scatter_plan* plan, const double* fields_host, 
  * behaviour; mask: prod(N) uint8 or NULL (voxels with mask == 0 get label -1);
  * labels: prod(N) int32, C order (x-major like product(range(imgx), range(imgy))).
  * Ties go to the lowest seed index (np.argmin).  stats_host (may be NULL) receives
- * [distance evaluations, tiles, overflowed tiles] after a stream sync when non-NULL. */
+ * [distance evaluations, tiles, overflowed tiles] after a stream sync when non-NULL.
+ * One-shot form: allocates and frees its workspace and synchronises `stream` before returning. */
 int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
                       const double* weights, int mode, const double* box_host,
                       const uint8_t* mask, int32_t* labels, void* stream, int64_t* stats_host);
+/* Plan form of the same call for repeated labellings of one grid size (sweeps): the plan owns the
+ * candidate-list workspace, execute is three kernel launches, asynchronous on `stream` unless
+ * stats_host is non-NULL.  A plan is bound to one device; executes on one plan must be issued in
+ * stream order (the workspace is reused). */
+typedef struct sbx_voronoi_plan sbx_voronoi_plan;
+int sbx_voronoi_plan_create(sbx_voronoi_plan** out, int device, int ndim, const int64_t* N);
+int sbx_voronoi_plan_execute(sbx_voronoi_plan* plan, const double* seeds, int64_t S,
+                             const double* weights, int mode, const double* box_host,
+                             const uint8_t* mask, int32_t* labels, void* stream,
+                             int64_t* stats_host);
+int sbx_voronoi_plan_destroy(sbx_voronoi_plan* plan);
 
 /* ---- one giant field across GPUs: slab-decomposed FFT + NCCL all-to-all ---------------
  * The reference cannot run a 1024^3 field (scatter.py:82-97 materialises ~300 B/voxel); its only

@@ -40,6 +40,9 @@ _SIGNATURES = {
     "sbx_scatter_peaks_execute": (C.c_int, [_vp, _vp, C.c_int, _vp, C.c_double, C.c_int, C.c_double, C.c_double, _vp, _vp, _vp, C.c_int, _vp]),
     "sbx_scatter_execute_host": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_double, C.c_int, C.c_double, C.c_double, _vp, _vp, C.c_int]),
     "sbx_voronoi_label": (C.c_int, [C.c_int, C.c_int, _i64p, _vp, C.c_int64, _vp, C.c_int, _f64p, _vp, _vp, _vp, _i64p]),
+    "sbx_voronoi_plan_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int, _i64p]),
+    "sbx_voronoi_plan_execute": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, _f64p, _vp, _vp, _vp, _i64p]),
+    "sbx_voronoi_plan_destroy": (C.c_int, [_vp]),
     "sbx_scatter_slab_plan_create": (C.c_int, [C.POINTER(_vp), _vp, C.c_int, C.c_int, C.c_int, _i64p, _f64p, C.c_int, C.c_double]),
     "sbx_scatter_slab_shells": (C.c_int, [_vp, C.POINTER(C.c_int), _f64p, _i64p]),
     "sbx_scatter_slab_execute": (C.c_int, [_vp, _vp, _vp, _vp]),

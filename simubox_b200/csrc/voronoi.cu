@@ -20,7 +20,9 @@
 // image is nearest everywhere (tiny boxes), power mode, and tiles whose candidate list overflows
 // fall back to a generic per-voxel evaluation of all three images per axis.
 #include <cstdint>
+#include <cstdlib>
 #include <cuda_runtime.h>
+#include <new>
 
 #include "common.h"
 
@@ -158,6 +160,58 @@ __device__ __forceinline__ double warp_min(double v) {
   return v;
 }
 
+// Bisector test (unweighted seeds): can B beat or tie A anywhere in the voxel box [lo, hi]?
+// d_B^2 - d_A^2 = sum_a e_a (s_a - 2 x_a) with e = B - A, s = B + A is affine in x, so its minimum over
+// the box is attained per axis at lo or hi.  UA = max over the box of d_A^2.  The 1e-11 relative
+// margin covers the rounding of this bound and of the reference's own evaluation, so a seed is
+// dropped only if it loses to A at every voxel of the box by far more than an ulp.
+template <int ND>
+__device__ __forceinline__ bool bisector_keep(const SeedRec& A, const SeedRec& B, const double lo[3], const double hi[3], double UA) {
+  double gmin = 0.0, scale = 0.0;
+  if (ND == 3) {
+    const double e = B.x - A.x, s = B.x + A.x;
+    gmin += fmin(e * (s - 2.0 * lo[0]), e * (s - 2.0 * hi[0]));
+    scale += fabs(e) * (fabs(A.x) + fabs(B.x) + 2.0 * hi[0] + 1.0);
+  }
+  {
+    const double e = B.y - A.y, s = B.y + A.y;
+    gmin += fmin(e * (s - 2.0 * lo[1]), e * (s - 2.0 * hi[1]));
+    scale += fabs(e) * (fabs(A.y) + fabs(B.y) + 2.0 * hi[1] + 1.0);
+  }
+  {
+    const double e = B.z - A.z, s = B.z + A.z;
+    gmin += fmin(e * (s - 2.0 * lo[2]), e * (s - 2.0 * hi[2]));
+    scale += fabs(e) * (fabs(A.z) + fabs(B.z) + 2.0 * hi[2] + 1.0);
+  }
+  return !(gmin > 1e-11 * (scale + UA + 1.0));  // also keeps NaN
+}
+
+template <int ND>
+__device__ __forceinline__ double box_max_d2(const SeedRec& A, const double lo[3], const double hi[3]) {
+  const double ax0 = A.x - lo[0], ax1 = A.x - hi[0], ay0 = A.y - lo[1], ay1 = A.y - hi[1], az0 = A.z - lo[2], az1 = A.z - hi[2];
+  return (ND == 3 ? fmax(ax0 * ax0, ax1 * ax1) : 0.0) + fmax(ay0 * ay0, ay1 * ay1) + fmax(az0 * az0, az1 * az1);
+}
+
+// warp argmin of squared distance to the point (cx, cy, cz) over the records rec[0..count)
+template <int ND>
+__device__ __forceinline__ int nearest_record(const SeedRec* rec, int count, double cx, double cy, double cz, int lane) {
+  double bd = INFINITY;
+  int bc = 0;
+  for (int c = lane; c < count; c += 32) {
+    const SeedRec R = rec[c];
+    const double dx = R.x - cx, dy = R.y - cy, dz = R.z - cz;
+    const double d2 = (ND == 3 ? dx * dx : 0.0) + dy * dy + dz * dz;
+    if (d2 < bd) { bd = d2; bc = c; }
+  }
+#pragma unroll
+  for (int off = 16; off > 0; off >>= 1) {
+    const double od = __shfl_xor_sync(kFull, bd, off);
+    const int oc = __shfl_xor_sync(kFull, bc, off);
+    if (od < bd || (od == bd && oc < bc)) { bd = od; bc = oc; }
+  }
+  return bc;
+}
+
 // ------------------------------------------------------------------------------------------
 // Coarse level: one CTA per coarse tile scans ALL seeds.  Seeds are taken interleaved (thread t,
 // round k -> seed 4096 c + 256 k + t: coalesced loads); lower bounds of a 4096-seed chunk are
@@ -252,12 +306,14 @@ coarse_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restri
 // and writes staged records + indices in ascending seed index.  rcount = count | generic flag.
 // ------------------------------------------------------------------------------------------
 template <int ND>
-__global__ void __launch_bounds__(128, 8)
+__global__ void __launch_bounds__(128, 6)
 mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* __restrict__ weights,
            const int* __restrict__ clist, const int* __restrict__ ccount, SeedRec* __restrict__ rec,
            int* __restrict__ ridx, int* __restrict__ rcount) {
   constexpr int kRounds = 8, kChunk = 32 * kRounds;
   __shared__ double s_lb[4][kChunk];
+  __shared__ alignas(16) SeedRec s_kr[4][kCap];  // records that passed the interval test, per warp
+  __shared__ int s_ki[4][kCap];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tile = blockIdx.x * 4 + warp;
   if (tile >= n_mid) return;
@@ -313,14 +369,21 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
           SeedRec r;
           r.x = pr[0]; r.y = pr[1]; r.z = pr[2];
           r.w = weights ? weights[s] : 0.0;
-          rec[(long long)tile * kCap + slot] = r;
-          ridx[(long long)tile * kCap + slot] = (int)s;
+          s_kr[warp][slot] = r;
+          s_ki[warp][slot] = (int)s;
         }
       }
       base += __popc(bal);
     }
   }
   const bool generic = __any_sync(kFull, any_amb) || g.mode == 1;
+  __syncwarp();
+  SeedRec* out_r = rec + (long long)tile * kCap;
+  int* out_i = ridx + (long long)tile * kCap;
+  for (int j = lane; j < min(base, kCap); j += 32) {
+    out_r[j] = s_kr[warp][j];
+    out_i[j] = s_ki[warp][j];
+  }
   if (lane == 0) rcount[tile] = base | (generic ? kFlagGeneric : 0);
 }
 
@@ -348,6 +411,9 @@ __device__ __forceinline__ double seed_value(const VorGeo& g, const double* __re
   return __dsub_rn(g.mode == 1 ? __dmul_rn(r, r) : r, w);
 }
 
+// rare path of the unweighted compare, kept out of line so that the inner loop stays small
+__device__ __noinline__ bool sqrt_less(double a, double b) { return __dsqrt_rn(a) < __dsqrt_rn(b); }
+
 // Warp / lane geometry of the label kernel.  A CTA of 8 warps labels HALF a mid tile (split along the
 // last axis).  3D: mid tile 16^3, half = 16 x 16 x 8 = 4 x 2 warps of 4 x 8 x 8 voxels;
 // 2D (1 x X x Y): mid tile 64 x 64, half = 64 x 32 = 2 x 4 warps of 32 x 8 pixels.  A lane owns one
@@ -368,20 +434,39 @@ template <> struct WarpTile<2> {
 // compare sums of squares and take the square root only when the two sums are within 8 ulps, where
 // rounding of the root could turn "smaller" into "equal" (then the lower index keeps the voxel, like
 // argmin).  MODE 2: additive with weights -- interval pruning, sqrt(ss) - w per candidate.
-template <int ND, int MODE>
-__global__ void __launch_bounds__(256, 3)
+template <int ND, int MODE, int CTAS>
+__global__ void __launch_bounds__(256, CTAS)
 label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
              const SeedRec* __restrict__ rec, const int* __restrict__ ridx, const int* __restrict__ rcount,
              const int* __restrict__ clist, const int* __restrict__ ccount, const uint8_t* __restrict__ mask,
-             int32_t* __restrict__ labels, unsigned long long* __restrict__ stats) {
+             int32_t* __restrict__ labels, unsigned long long* __restrict__ stats, int pf_planes) {
   using WT = WarpTile<ND>;
   __shared__ alignas(128) SeedRec s_rec[kCap];
   __shared__ alignas(16) int s_idx[kCap];
   __shared__ alignas(16) double s_dz[8][32];      // per warp: (z_c - z_k)^2 of a batch of 4 candidates x 8 voxels
   __shared__ unsigned char s_list[8][kCap];       // per warp: surviving record slots, ascending
   __shared__ alignas(8) uint64_t s_bar;
-  const int tile = blockIdx.x >> 1, half = blockIdx.x & 1;
+  // grid = (2 * nm[2], nm[1], nm[0]): no integer division to find the tile
+  const int t[3] = {(int)blockIdx.z, (int)blockIdx.y, (int)(blockIdx.x >> 1)};
+  const int half = blockIdx.x & 1;
+  const int tile = (t[0] * g.nm[1] + t[1]) * g.nm[2] + t[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  int o[3], lx, ly;
+  WT::origin(warp, half, o);
+  WT::lane_xy(lane, lx, ly);
+  const int x0 = t[0] * WT::M0 + o[0], y0 = t[1] * WT::M1 + o[1], z0 = t[2] * WT::M2 + o[2];
+  const bool w_in = x0 < g.N[0] && y0 < g.N[1] && z0 < g.N[2];
+  const int vx = x0 + lx, vy = y0 + ly;
+  const bool col_in = w_in && vx < g.N[0] && vy < g.N[1];
+  const int nz = min(kCol, g.N[2] - z0);
+  const long long lin = ((long long)vx * g.N[1] + vy) * g.N[2] + z0;
+  const bool mfast = mask && col_in && nz == kCol && (reinterpret_cast<uintptr_t>(mask + lin) & 7) == 0;
+  uint2 mraw = make_uint2(0u, 0u);
+  if (mfast) mraw = __ldg(reinterpret_cast<const uint2*>(mask + lin));  // issued first: the longest latency of the CTA
+  if (mask && col_in && pf_planes > 0 && vx + pf_planes < g.N[0]) {
+    // pull the mask bytes of the CTA that runs about one wave later (same y/z, pf_planes further along x) into L2
+    asm volatile("prefetch.global.L2 [%0];" ::"l"(mask + lin + (long long)pf_planes * g.N[1] * g.N[2]));
+  }
   const int raw = rcount[tile];
   const int count = raw & (kFlagGeneric - 1);
   const bool generic = MODE == 0 || (raw & kFlagGeneric) != 0;
@@ -396,28 +481,17 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
     tma_bulk_g2s(s_idx, ridx + (long long)tile * kCap, b_idx, &s_bar);
   }
 
-  int t[3], o[3], lx, ly;
-  tile_coords(g.nm, tile, t);
-  WT::origin(warp, half, o);
-  WT::lane_xy(lane, lx, ly);
-  const int x0 = t[0] * WT::M0 + o[0], y0 = t[1] * WT::M1 + o[1], z0 = t[2] * WT::M2 + o[2];
-  if (x0 >= g.N[0] || y0 >= g.N[1] || z0 >= g.N[2]) return;  // whole warp outside the grid (no CTA barrier follows)
-  const int vx = x0 + lx, vy = y0 + ly;
-  const bool col_in = vx < g.N[0] && vy < g.N[1];
-  const int nz = min(kCol, g.N[2] - z0);
-  const long long lin = ((long long)vx * g.N[1] + vy) * g.N[2] + z0;
+  if (!w_in) return;  // whole warp outside the grid (no CTA barrier follows)
   unsigned live = col_in ? (1u << nz) - 1u : 0u;
   if (mask && col_in) {
-    if (nz == kCol && (reinterpret_cast<uintptr_t>(mask + lin) & 7) == 0) {
-      const uint2 mm = *reinterpret_cast<const uint2*>(mask + lin);
-      live = 0;
+    live = 0;
+    if (mfast) {
 #pragma unroll
       for (int k = 0; k < 4; ++k) {
-        if ((mm.x >> (8 * k)) & 0xffu) live |= 1u << k;
-        if ((mm.y >> (8 * k)) & 0xffu) live |= 1u << (k + 4);
+        if ((mraw.x >> (8 * k)) & 0xffu) live |= 1u << k;
+        if ((mraw.y >> (8 * k)) & 0xffu) live |= 1u << (k + 4);
       }
     } else {
-      live = 0;
       for (int k = 0; k < nz; ++k)
         if (mask[lin + k]) live |= 1u << k;
     }
@@ -465,51 +539,12 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
       int kept = 0;
       if (MODE == 1) {
         // reference seed A: nearest to the sub-tile centre
-        const double cx = 0.5 * (lo[0] + hi[0]), cy = 0.5 * (lo[1] + hi[1]), cz = 0.5 * (lo[2] + hi[2]);
-        double bd = INFINITY;
-        int bc = 0;
-        for (int r = 0; r < rounds; ++r) {
-          const int c = 32 * r + lane;
-          if (c < count) {
-            const SeedRec R = s_rec[c];
-            const double dx = R.x - cx, dy = R.y - cy, dz = R.z - cz;
-            const double d2 = (ND == 3 ? dx * dx : 0.0) + dy * dy + dz * dz;
-            if (d2 < bd) { bd = d2; bc = c; }
-          }
-        }
-#pragma unroll
-        for (int off = 16; off > 0; off >>= 1) {
-          const double od = __shfl_xor_sync(kFull, bd, off);
-          const int oc = __shfl_xor_sync(kFull, bc, off);
-          if (od < bd || (od == bd && oc < bc)) { bd = od; bc = oc; }
-        }
+        const int bc = nearest_record<ND>(s_rec, count, 0.5 * (lo[0] + hi[0]), 0.5 * (lo[1] + hi[1]), 0.5 * (lo[2] + hi[2]), lane);
         const SeedRec A = s_rec[bc];
-        const double ax0 = A.x - lo[0], ax1 = A.x - hi[0], ay0 = A.y - lo[1], ay1 = A.y - hi[1], az0 = A.z - lo[2], az1 = A.z - hi[2];
-        const double UA = (ND == 3 ? fmax(ax0 * ax0, ax1 * ax1) : 0.0) + fmax(ay0 * ay0, ay1 * ay1) + fmax(az0 * az0, az1 * az1);
+        const double UA = box_max_d2<ND>(A, lo, hi);
         for (int r = 0; r < rounds; ++r) {
           const int c = 32 * r + lane;
-          bool keep = false;
-          if (c < count) {
-            const SeedRec B = s_rec[c];
-            // min over the box of d_B^2 - d_A^2 = sum_a e_a (s_a - 2 x_a),  e = B - A,  s = B + A
-            double gmin = 0.0, scale = 0.0;
-            if (ND == 3) {
-              const double e = B.x - A.x, s = B.x + A.x;
-              gmin += fmin(e * (s - 2.0 * lo[0]), e * (s - 2.0 * hi[0]));
-              scale += fabs(e) * (fabs(A.x) + fabs(B.x) + 2.0 * hi[0] + 1.0);
-            }
-            {
-              const double e = B.y - A.y, s = B.y + A.y;
-              gmin += fmin(e * (s - 2.0 * lo[1]), e * (s - 2.0 * hi[1]));
-              scale += fabs(e) * (fabs(A.y) + fabs(B.y) + 2.0 * hi[1] + 1.0);
-            }
-            {
-              const double e = B.z - A.z, s = B.z + A.z;
-              gmin += fmin(e * (s - 2.0 * lo[2]), e * (s - 2.0 * hi[2]));
-              scale += fabs(e) * (fabs(A.z) + fabs(B.z) + 2.0 * hi[2] + 1.0);
-            }
-            keep = !(gmin > 1e-11 * (scale + UA + 1.0));  // B beats or ties A somewhere in the box (or NaN)
-          }
+          const bool keep = c < count && bisector_keep<ND>(A, s_rec[c], lo, hi, UA);
           const unsigned bal = __ballot_sync(kFull, keep);
           if (keep) s_list[warp][kept + __popc(bal & ((1u << lane) - 1u))] = (unsigned char)c;
           kept += __popc(bal);
@@ -584,9 +619,10 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
               const double ss = __dadd_rn(sxy, q ? d2.y : d2.x);
               if (MODE == 1) {
                 bool take = ss < bs[k];
-                // sums within 8 ulps: their roots may round together, then the earlier index stays
-                if (take && __double_as_longlong(bs[k]) - __double_as_longlong(ss) <= 8) take = __dsqrt_rn(ss) < __dsqrt_rn(bs[k]);
-                if (take) { bs[k] = ss; bi[k] = idx; }
+                // sums within 8 ulps: their roots may round together, then the earlier index stays (rare branch)
+                if (take && __double_as_longlong(bs[k]) - __double_as_longlong(ss) <= 8) take = sqrt_less(ss, bs[k]);
+                bs[k] = take ? ss : bs[k];
+                bi[k] = take ? idx : bi[k];
               } else {
                 const double val = __dsub_rn(__dsqrt_rn(ss), w);
                 if (val < bs[k] || bi[k] < 0) { bs[k] = val; bi[k] = idx; }
@@ -632,34 +668,59 @@ static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, c
                            int32_t* labels, unsigned long long* stats, cudaStream_t st) {
   coarse_kernel<ND><<<(unsigned)ctiles, 256, 0, st>>>(g, seeds, weights, clist, ccount);
   mid_kernel<ND><<<(unsigned)((tiles + 3) / 4), 128, 0, st>>>(g, (int)tiles, seeds, weights, clist, ccount, rec, ridx, rcount);
-  if (g.mode == 1)
-    label_kernel<ND, 0><<<(unsigned)tiles * 2, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
-  else if (!weights)
-    label_kernel<ND, 1><<<(unsigned)tiles * 2, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
-  else
-    label_kernel<ND, 2><<<(unsigned)tiles * 2, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+  const dim3 lgrid((unsigned)(2 * g.nm[2]), (unsigned)g.nm[1], (unsigned)g.nm[0]);
+  // CTAs per axis-0 tile layer; prefetch distance = as many layers as hold about one wave (3-4 CTAs x 148 SMs)
+  const long long per_layer = (long long)lgrid.x * lgrid.y;
+  static const int pf_on = [] { const char* e = getenv("SBX_VOR_PF"); return e ? atoi(e) : 1; }();
+  const int pf_planes = pf_on ? (int)((600 + per_layer - 1) / per_layer) * g.M[0] : 0;
+  static const int ctas = [] { const char* e = getenv("SBX_LABEL_CTAS"); return e ? atoi(e) : 3; }();
+#define SBX_LABEL(MODE)                                                                                              \
+  do {                                                                                                               \
+    if (ctas == 4)                                                                                                   \
+      label_kernel<ND, MODE, 4><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats, pf_planes); \
+    else                                                                                                             \
+      label_kernel<ND, MODE, 3><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats, pf_planes); \
+  } while (0)
+  if (g.mode == 1) SBX_LABEL(0);
+  else if (!weights) SBX_LABEL(1);
+  else SBX_LABEL(2);
+#undef SBX_LABEL
 }
 
-extern "C" int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
-                                 const double* weights, int mode, const double* box_host, const uint8_t* mask,
-                                 int32_t* labels, void* stream, int64_t* stats_host) {
-  if (!N || !seeds || !labels) return fail(SBX_EINVAL, "NULL argument");
+// A plan owns the per-grid workspace (candidate lists of the coarse and mid tiles), so that repeated
+// labellings of one grid size cost three kernel launches and nothing else on the host.
+struct sbx_voronoi_plan {
+  int device = 0, ndim = 3;
+  VorGeo g{};
+  long long tiles = 1, ctiles = 1;
+  SeedRec* rec = nullptr;
+  int *ridx = nullptr, *rcount = nullptr, *clist = nullptr, *ccount = nullptr;
+  unsigned long long* stats = nullptr;
+};
+
+extern "C" int sbx_voronoi_plan_destroy(sbx_voronoi_plan* p) {
+  if (!p) return SBX_OK;
+  DeviceGuard guard(p->device);
+  cudaFree(p->rec); cudaFree(p->ridx); cudaFree(p->rcount); cudaFree(p->clist); cudaFree(p->ccount); cudaFree(p->stats);
+  delete p;
+  return SBX_OK;
+}
+
+extern "C" int sbx_voronoi_plan_create(sbx_voronoi_plan** out, int device, int ndim, const int64_t* N) {
+  if (!out || !N) return fail(SBX_EINVAL, "NULL argument");
+  *out = nullptr;
   if (ndim != 2 && ndim != 3) return fail(SBX_EINVAL, "ndim must be 2 or 3, got %d", ndim);
-  if (S < 1 || S > 0x3fffffff) return fail(SBX_EINVAL, "seed count %lld out of range", (long long)S);
-  if (mode != 0 && mode != 1) return fail(SBX_EINVAL, "mode must be 0 (additive) or 1 (power)");
   int rc = require_sm100(device);
   if (rc) return rc;
   DeviceGuard guard(device);
-  cudaStream_t st = (cudaStream_t)stream;
-
-  VorGeo g{};
+  sbx_voronoi_plan* p = new (std::nothrow) sbx_voronoi_plan();
+  if (!p) return fail(SBX_ENOMEM, "out of host memory");
+  p->device = device;
+  p->ndim = ndim;
+  VorGeo& g = p->g;
   g.nd = ndim;
-  g.mode = mode;
-  g.S = S;
-  g.periodic = box_host ? 1 : 0;
   const int mid3[3] = {16, 16, 16}, mid2[3] = {1, 64, 64};
   const int coarse3[3] = {32, 32, 32}, coarse2[3] = {1, 256, 256};
-  long long tiles = 1, ctiles = 1;
   const int off = 3 - ndim;  // internal axis of real axis 0
   for (int a = 0; a < 3; ++a) {
     g.N[a] = 1;
@@ -668,47 +729,79 @@ extern "C" int sbx_voronoi_label(int device, int ndim, const int64_t* N, const d
     g.C[a] = ndim == 3 ? coarse3[a] : coarse2[a];
   }
   for (int a = 0; a < ndim; ++a) {
-    if (N[a] < 1 || N[a] > (1 << 20)) return fail(SBX_EINVAL, "N[%d]=%lld out of range", a, (long long)N[a]);
+    if (N[a] < 1 || N[a] > (1 << 20)) { delete p; return fail(SBX_EINVAL, "N[%d]=%lld out of range", a, (long long)N[a]); }
     g.N[a + off] = (int)N[a];
-    if (box_host) {
-      if (!(box_host[a] > 0.0)) return fail(SBX_EINVAL, "box[%d] must be > 0", a);
-      g.box[a + off] = box_host[a];
-    }
   }
   for (int a = 0; a < 3; ++a) {
     g.nm[a] = (g.N[a] + g.M[a] - 1) / g.M[a];
     g.nc[a] = (g.N[a] + g.C[a] - 1) / g.C[a];
-    tiles *= g.nm[a];
-    ctiles *= g.nc[a];
+    p->tiles *= g.nm[a];
+    p->ctiles *= g.nc[a];
   }
-  if (tiles > 0x3fffffff) return fail(SBX_EINVAL, "grid too large (%lld tiles)", tiles);
+  if (p->tiles > 0x3fffffff || g.nm[0] > 65535 || g.nm[1] > 65535) {
+    const long long t = p->tiles;
+    delete p;
+    return fail(SBX_EINVAL, "grid too large (%lld tiles)", t);
+  }
+  cudaError_t e = cudaMalloc((void**)&p->rec, (size_t)p->tiles * kCap * sizeof(SeedRec));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&p->ridx, (size_t)p->tiles * kCap * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&p->rcount, (size_t)p->tiles * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&p->clist, (size_t)p->ctiles * kCoarseCap * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&p->ccount, (size_t)p->ctiles * sizeof(int));
+  if (e == cudaSuccess) e = cudaMalloc((void**)&p->stats, 3 * sizeof(unsigned long long));
+  if (e != cudaSuccess) {
+    sbx_voronoi_plan_destroy(p);
+    return fail(e == cudaErrorMemoryAllocation ? SBX_ENOMEM : SBX_ECUDA, "voronoi plan allocation: %s", cudaGetErrorString(e));
+  }
+  *out = p;
+  return SBX_OK;
+}
 
-  SeedRec* rec = nullptr;
-  int *ridx = nullptr, *rcount = nullptr, *clist = nullptr, *ccount = nullptr;
-  unsigned long long* stats = nullptr;
-  SBX_CUDA(cudaMallocAsync((void**)&rec, (size_t)tiles * kCap * sizeof(SeedRec), st));
-  SBX_CUDA(cudaMallocAsync((void**)&ridx, (size_t)tiles * kCap * sizeof(int), st));
-  SBX_CUDA(cudaMallocAsync((void**)&rcount, (size_t)tiles * sizeof(int), st));
-  SBX_CUDA(cudaMallocAsync((void**)&clist, (size_t)ctiles * kCoarseCap * sizeof(int), st));
-  SBX_CUDA(cudaMallocAsync((void**)&ccount, (size_t)ctiles * sizeof(int), st));
-  if (stats_host) {
-    SBX_CUDA(cudaMallocAsync((void**)&stats, 3 * sizeof(unsigned long long), st));
-    SBX_CUDA(cudaMemsetAsync(stats, 0, 3 * sizeof(unsigned long long), st));
+extern "C" int sbx_voronoi_plan_execute(sbx_voronoi_plan* p, const double* seeds, int64_t S, const double* weights,
+                                        int mode, const double* box_host, const uint8_t* mask, int32_t* labels,
+                                        void* stream, int64_t* stats_host) {
+  if (!p || !seeds || !labels) return fail(SBX_EINVAL, "NULL argument");
+  if (S < 1 || S > 0x3fffffff) return fail(SBX_EINVAL, "seed count %lld out of range", (long long)S);
+  if (mode != 0 && mode != 1) return fail(SBX_EINVAL, "mode must be 0 (additive) or 1 (power)");
+  DeviceGuard guard(p->device);
+  cudaStream_t st = (cudaStream_t)stream;
+  VorGeo g = p->g;
+  g.mode = mode;
+  g.S = S;
+  g.periodic = box_host ? 1 : 0;
+  const int off = 3 - p->ndim;
+  for (int a = 0; a < p->ndim && box_host; ++a) {
+    if (!(box_host[a] > 0.0)) return fail(SBX_EINVAL, "box[%d] must be > 0", a);
+    g.box[a + off] = box_host[a];
   }
-  if (ndim == 3) launch_voronoi<3>(g, ctiles, tiles, seeds, weights, clist, ccount, rec, ridx, rcount, mask, labels, stats, st);
-  else launch_voronoi<2>(g, ctiles, tiles, seeds, weights, clist, ccount, rec, ridx, rcount, mask, labels, stats, st);
+  unsigned long long* stats = stats_host ? p->stats : nullptr;
+  if (stats) SBX_CUDA(cudaMemsetAsync(stats, 0, 3 * sizeof(unsigned long long), st));
+  if (p->ndim == 3)
+    launch_voronoi<3>(g, p->ctiles, p->tiles, seeds, weights, p->clist, p->ccount, p->rec, p->ridx, p->rcount, mask, labels, stats, st);
+  else
+    launch_voronoi<2>(g, p->ctiles, p->tiles, seeds, weights, p->clist, p->ccount, p->rec, p->ridx, p->rcount, mask, labels, stats, st);
   SBX_CUDA(cudaGetLastError());
   if (stats_host) {
     unsigned long long h[3];
     SBX_CUDA(cudaMemcpyAsync(h, stats, sizeof(h), cudaMemcpyDeviceToHost, st));
     SBX_CUDA(cudaStreamSynchronize(st));
     for (int i = 0; i < 3; ++i) stats_host[i] = (int64_t)h[i];
-    SBX_CUDA(cudaFreeAsync(stats, st));
   }
-  SBX_CUDA(cudaFreeAsync(rec, st));
-  SBX_CUDA(cudaFreeAsync(ridx, st));
-  SBX_CUDA(cudaFreeAsync(rcount, st));
-  SBX_CUDA(cudaFreeAsync(clist, st));
-  SBX_CUDA(cudaFreeAsync(ccount, st));
   return SBX_OK;
+}
+
+// one-shot convenience: plan + execute + destroy (synchronises `stream` before the workspace is freed)
+extern "C" int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
+                                 const double* weights, int mode, const double* box_host, const uint8_t* mask,
+                                 int32_t* labels, void* stream, int64_t* stats_host) {
+  sbx_voronoi_plan* p = nullptr;
+  int rc = sbx_voronoi_plan_create(&p, device, ndim, N);
+  if (rc) return rc;
+  rc = sbx_voronoi_plan_execute(p, seeds, S, weights, mode, box_host, mask, labels, stream, stats_host);
+  {
+    DeviceGuard guard(device);
+    cudaStreamSynchronize((cudaStream_t)stream);
+  }
+  sbx_voronoi_plan_destroy(p);
+  return rc;
 }

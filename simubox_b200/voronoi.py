@@ -21,6 +21,37 @@ from .reader import parse_density
 from .schema import ColorMode, Density, OpenCVResult, WeightedMode
 
 _MODES = {"additive": 0, "power": 1}
+_PLANS: dict = {}
+
+
+class _VoronoiPlan:
+    """Owner of an ``sbx_voronoi_plan`` (candidate-list workspace of one grid size on one device)."""
+
+    def __init__(self, device: int, shape):
+        self._h = C.c_void_p()
+        self._keep, pn = _lib.i64(shape)
+        _lib.check(_lib.lib().sbx_voronoi_plan_create(C.byref(self._h), int(device), len(shape), pn))
+
+    def close(self):
+        if self._h:
+            _lib.lib().sbx_voronoi_plan_destroy(self._h)
+            self._h = C.c_void_p()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def _get_plan(device: int, shape) -> _VoronoiPlan:
+    key = (int(device), tuple(shape))
+    plan = _PLANS.get(key)
+    if plan is None:
+        if len(_PLANS) >= 8:
+            _PLANS.pop(next(iter(_PLANS))).close()
+        plan = _PLANS[key] = _VoronoiPlan(device, shape)
+    return plan
 
 
 def _mode_id(method) -> int:
@@ -78,15 +109,15 @@ class VoronoiCell:
             if tuple(m.shape) != shape:
                 raise ValueError(f"mask shape {tuple(m.shape)} != grid {shape}")
         labels = torch.empty(shape, dtype=torch.int32, device=pts.device)
-        _, pn = _lib.i64(shape)
         pb = None
         if box is not None:
             _keep, pb = _lib.f64(box)
             if len(_keep) != nd:
                 raise ValueError(f"box must have {nd} entries")
         st_arr = np.zeros(3, dtype=np.int64) if stats else None
-        _lib.check(_lib.lib().sbx_voronoi_label(
-            device, nd, pn, ptr(pts), S, ptr(w), _mode_id(method), pb, ptr(m), ptr(labels), stream_ptr(device),
+        plan = _get_plan(device, shape)
+        _lib.check(_lib.lib().sbx_voronoi_plan_execute(
+            plan._h, ptr(pts), S, ptr(w), _mode_id(method), pb, ptr(m), ptr(labels), stream_ptr(device),
             st_arr.ctypes.data_as(C.POINTER(C.c_int64)) if stats else None))
         out = labels if return_tensor else labels.cpu().numpy()
         if stats:

@@ -94,3 +94,23 @@ def test_baseline_config_256_cubed_4096_seeds(sbx_lib):
     same = (torch.roll(full_t, shifts=(32, 0, 64), dims=(0, 1, 2)) == shifted).float().mean().item()
     assert same > 0.9999  # not bit-identical: (p + L) - x rounds differently from p - x on exact-tie voxels
     assert st["evaluations"] / max(int(m.sum()), 1) < 64
+
+
+def test_one_shot_c_entry_point(sbx_lib):
+    """sbx_voronoi_label (plan + execute + destroy in one call) straight through ctypes."""
+    import ctypes as C
+
+    import torch
+
+    rng = np.random.default_rng(5)
+    shape = (20, 24, 18)
+    pts = rng.uniform(0, 18, (30, 3))
+    d_pts = torch.from_numpy(pts).cuda()
+    lab = torch.empty(shape, dtype=torch.int32, device="cuda")
+    _, pn = sbx_lib.i64(shape)
+    _, pb = sbx_lib.f64([float(n) for n in shape])
+    st = np.zeros(3, dtype=np.int64)
+    sbx_lib.check(sbx_lib.lib().sbx_voronoi_label(0, 3, pn, C.c_void_p(d_pts.data_ptr()), 30, None, 0, pb, None,
+                                                  C.c_void_p(lab.data_ptr()), None, st.ctypes.data_as(C.POINTER(C.c_int64))))
+    ref = voronoi_np.label_grid(pts, 0, shape, box=tuple(float(n) for n in shape))
+    assert np.array_equal(lab.cpu().numpy(), ref) and st[1] > 0
