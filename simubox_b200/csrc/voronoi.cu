@@ -434,12 +434,12 @@ template <> struct WarpTile<2> {
 // compare sums of squares and take the square root only when the two sums are within 8 ulps, where
 // rounding of the root could turn "smaller" into "equal" (then the lower index keeps the voxel, like
 // argmin).  MODE 2: additive with weights -- interval pruning, sqrt(ss) - w per candidate.
-template <int ND, int MODE, int CTAS>
-__global__ void __launch_bounds__(256, CTAS)
+template <int ND, int MODE>
+__global__ void __launch_bounds__(256, 3)
 label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
              const SeedRec* __restrict__ rec, const int* __restrict__ ridx, const int* __restrict__ rcount,
              const int* __restrict__ clist, const int* __restrict__ ccount, const uint8_t* __restrict__ mask,
-             int32_t* __restrict__ labels, unsigned long long* __restrict__ stats, int pf_planes) {
+             int32_t* __restrict__ labels, unsigned long long* __restrict__ stats) {
   using WT = WarpTile<ND>;
   __shared__ alignas(128) SeedRec s_rec[kCap];
   __shared__ alignas(16) int s_idx[kCap];
@@ -463,10 +463,6 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
   const bool mfast = mask && col_in && nz == kCol && (reinterpret_cast<uintptr_t>(mask + lin) & 7) == 0;
   uint2 mraw = make_uint2(0u, 0u);
   if (mfast) mraw = __ldg(reinterpret_cast<const uint2*>(mask + lin));  // issued first: the longest latency of the CTA
-  if (mask && col_in && pf_planes > 0 && vx + pf_planes < g.N[0]) {
-    // pull the mask bytes of the CTA that runs about one wave later (same y/z, pf_planes further along x) into L2
-    asm volatile("prefetch.global.L2 [%0];" ::"l"(mask + lin + (long long)pf_planes * g.N[1] * g.N[2]));
-  }
   const int raw = rcount[tile];
   const int count = raw & (kFlagGeneric - 1);
   const bool generic = MODE == 0 || (raw & kFlagGeneric) != 0;
@@ -669,22 +665,12 @@ static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, c
   coarse_kernel<ND><<<(unsigned)ctiles, 256, 0, st>>>(g, seeds, weights, clist, ccount);
   mid_kernel<ND><<<(unsigned)((tiles + 3) / 4), 128, 0, st>>>(g, (int)tiles, seeds, weights, clist, ccount, rec, ridx, rcount);
   const dim3 lgrid((unsigned)(2 * g.nm[2]), (unsigned)g.nm[1], (unsigned)g.nm[0]);
-  // CTAs per axis-0 tile layer; prefetch distance = as many layers as hold about one wave (3-4 CTAs x 148 SMs)
-  const long long per_layer = (long long)lgrid.x * lgrid.y;
-  static const int pf_on = [] { const char* e = getenv("SBX_VOR_PF"); return e ? atoi(e) : 1; }();
-  const int pf_planes = pf_on ? (int)((600 + per_layer - 1) / per_layer) * g.M[0] : 0;
-  static const int ctas = [] { const char* e = getenv("SBX_LABEL_CTAS"); return e ? atoi(e) : 3; }();
-#define SBX_LABEL(MODE)                                                                                              \
-  do {                                                                                                               \
-    if (ctas == 4)                                                                                                   \
-      label_kernel<ND, MODE, 4><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats, pf_planes); \
-    else                                                                                                             \
-      label_kernel<ND, MODE, 3><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats, pf_planes); \
-  } while (0)
-  if (g.mode == 1) SBX_LABEL(0);
-  else if (!weights) SBX_LABEL(1);
-  else SBX_LABEL(2);
-#undef SBX_LABEL
+  if (g.mode == 1)
+    label_kernel<ND, 0><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+  else if (!weights)
+    label_kernel<ND, 1><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+  else
+    label_kernel<ND, 2><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
 }
 
 // A plan owns the per-grid workspace (candidate lists of the coarse and mid tiles), so that repeated
