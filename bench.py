@@ -219,7 +219,7 @@ def run_scatter(args):
         nb = min(16, B - b0)
         fields[b0:b0 + nb] = synth.fields_torch(rank * B + b0, nb, shape, cells=cells, device=dev)
     torch.cuda.synchronize()
-    path = {"auto": 0, "dense": 1, "gather": 2, "pruned": 3}[args.path]
+    path = {"auto": 0, "dense": 1, "gather": 2, "pruned": 3, "fused": 4}[args.path]
     kw = dict(cutoff=30, threshold=1e-12, peaks=True, width=PEAK_KW["width"], step=PEAK_KW["step"],
               peak_cutoff=PEAK_KW["cutoff"], min_height=PEAK_KW["min_height"], max_batch=args.max_batch, device=local, path=path)
     plan = get_plan(shape, L, 30, 1e-12, max_batch=min(args.max_batch, B), device=local, path=path)
@@ -278,7 +278,11 @@ def run_scatter(args):
     spec_bytes = 16 * n * n * (n // 2 + 1)
     pipeline_bytes = 8 * n ** 3 + 2 * spec_bytes
     pathname = _lib.PATH_NAMES[plan.path]
-    if plan.path == 3:  # pruned DFT: pruned_planes_kernel reads each field exactly once (first event pair)
+    if plan.path == 4:  # fused pruned DFT: ONE kernel reads each field exactly once and finishes it
+        kern, unit_bytes = "pruned_fused_kernel", 8 * n ** 3
+        launches_per_step = own_per_step
+        fused_ms_per_launch = prof["transform_ms"] / max(prof["own_launches"], 1)
+    elif plan.path == 3:  # pruned DFT: pruned_planes_kernel reads each field exactly once (first event pair)
         kern, unit_bytes = "pruned_planes_kernel", 8 * n ** 3
         launches_per_step = own_per_step / 2
         fused_ms_per_launch = prof["transform_ms"] / max(prof["own_launches"] / 2, 1)
@@ -291,7 +295,8 @@ def run_scatter(args):
             "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
             "algorithmic_bytes_per_field": unit_bytes, "fields_per_launch": fields_per_launch,
             "kernel_ms_per_launch": fused_ms_per_launch,
-            "step_split_ms": ({"pruned_planes_kernel": transform_ms_per_step, "pruned_finish_kernel": fused_ms_per_step} if plan.path == 3
+            "step_split_ms": ({"pruned_fused_kernel": transform_ms_per_step} if plan.path == 4 else
+                              {"pruned_planes_kernel": transform_ms_per_step, "pruned_finish_kernel": fused_ms_per_step} if plan.path == 3
                               else {"transform(cuFFT)": transform_ms_per_step, "own_kernels": fused_ms_per_step}),
             "pipeline": {"bytes_per_field": pipeline_bytes, "achieved": pipeline_bytes * B / (ms * 1e-3) / 1e9,
                          "frac": pipeline_bytes * B / (ms * 1e-3) / 1e9 / peak}}
@@ -467,7 +472,7 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
     ap.add_argument("--workload", default="scatter", choices=["scatter", "voronoi"])
-    ap.add_argument("--path", default="auto", choices=["auto", "dense", "gather", "pruned"])
+    ap.add_argument("--path", default="auto", choices=["auto", "dense", "gather", "pruned", "fused"])
     ap.add_argument("--grid", type=int, default=128)
     ap.add_argument("--cells", type=int, default=2)
     ap.add_argument("--fields", type=int, default=256)

@@ -47,7 +47,10 @@ enum {
   SBX_SCATTER_AUTO = 0,       /* choose the fastest valid path                                */
   SBX_SCATTER_FFT_DENSE = 1,  /* cuFFT D2Z + fused full-spectrum |F|^2/shell-histogram kernel */
   SBX_SCATTER_FFT_GATHER = 2, /* cuFFT D2Z + fused gather of the shell members only           */
-  SBX_SCATTER_PRUNED = 3      /* hand-written pruned DFT of the member modes (no spectrum)    */
+  SBX_SCATTER_PRUNED = 3,     /* hand-written pruned DFT of the member modes (no spectrum),
+                                 two kernels: planes + finish                                  */
+  SBX_SCATTER_PRUNED_FUSED = 4 /* the same in ONE kernel: folded z stage, x accumulation in
+                                 registers, finish by the last CTA of each field               */
 };
 
 typedef struct sbx_scatter_plan sbx_scatter_plan;

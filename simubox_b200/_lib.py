@@ -15,8 +15,8 @@ PKG = Path(__file__).resolve().parent
 LIB_PATH = Path(os.environ.get("SIMUBOX_B200_LIB", PKG / "libsimubox_b200.so"))
 
 SBX_DEVICE_NONE = -1
-PATH_AUTO, PATH_DENSE, PATH_GATHER, PATH_PRUNED = 0, 1, 2, 3
-PATH_NAMES = {0: "auto", 1: "fft_dense", 2: "fft_gather", 3: "pruned_dft"}
+PATH_AUTO, PATH_DENSE, PATH_GATHER, PATH_PRUNED, PATH_PRUNED_FUSED = 0, 1, 2, 3, 4
+PATH_NAMES = {0: "auto", 1: "fft_dense", 2: "fft_gather", 3: "pruned_dft", 4: "pruned_dft_fused"}
 
 _i64p = C.POINTER(C.c_int64)
 _f64p = C.POINTER(C.c_double)

@@ -37,13 +37,20 @@ __device__ inline void peaks_block(const double* __restrict__ q, const double* _
   const int tid = threadIdx.x, nthr = blockDim.x;
   const int lane = tid & 31, warp = tid >> 5, nwarp = (nthr + 31) >> 5;
 
-  if (tid == 0) {  // q_Intensity[q_Intensity[:,0] <= cutoff]  (scatter.py:141)
+  // stage q and I in shared memory with parallel loads (a serial walk over global memory costs one L2
+  // round trip per row), then compact in order:  q_Intensity[q_Intensity[:,0] <= cutoff]  (scatter.py:141)
+  for (int r = tid; r < n; r += nthr) {
+    amp[r] = q[r];
+    ctr[r] = r == 0 ? 0.0 : I[r];  // scatter.py:138
+  }
+  __syncthreads();
+  if (tid == 0) {
     int m = 0;
-    for (int r = 0; r < n; ++r) {
-      const double qr = q[r];
+    for (int r = 0; r < n; ++r) {  // m <= r: slot m is rewritten only after row r has been read
+      const double qr = amp[r], ir = ctr[r];
       if (qr <= pp.q_cutoff) {
         ctr[m] = qr;
-        amp[m] = r == 0 ? 0.0 : I[r];  // scatter.py:138
+        amp[m] = ir;
         ++m;
       }
     }

@@ -1,0 +1,432 @@
+// pruned_fused.cuh -- single-kernel pruned DFT: folded z stage, y stage, x accumulation, per-field
+// finish (|F|^2/N, shell sums, peaks) by the last CTA that touches the field (sm_100a).
+//
+// Same mathematics as pruned_dft.cuh (the low-|q| modes the shell table of
+// SimuBox/calculator/scatter.py:99-115 keeps, out of the full FFT of :85), with two changes:
+//
+//  * radix-2 fold along z: with e[z] = rho[z] + rho[z + N2/2], o[z] = rho[z] - rho[z + N2/2]
+//    (z < N2/2), the even frequencies c = 0,2,4,6 are sums over e and the odd ones over o, because
+//    exp(-2 pi i c (z + N2/2) / N2) = (-1)^c exp(-2 pi i c z / N2).  Two 8-column DMMA tiles over
+//    K = N2/2 replace one 16-column product over K = N2: half the tensor instructions per byte
+//    loaded, and both halves of a row are read with forward, 16-byte aligned loads.
+//  * the x transform is accumulated plane by plane in registers (one thread per listed mode), so the
+//    per-plane 16x16 results never go to HBM.  A work unit = `xc` consecutive planes of one field;
+//    units are handed out by an atomic counter; a unit ends by writing its partial sums; the CTA that
+//    completes a field (ticket) adds the partials in fixed order -- the result does not depend on the
+//    schedule -- and runs the shell sums and the peak search.
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "peaks.cuh"
+#include "pruned_dft.cuh"
+
+namespace sbx {
+
+constexpr int kFusedModesPerThread = 2;  // listed modes <= 2 * 256
+
+struct FusedArgs {
+  const double* fields;
+  int n_fields;
+  int N0, N1, N2;
+  int ks1;            // stage-2 k-steps: N1 / 4
+  int gstride;        // N1 + 4
+  int ds;             // fold steps: N2 / 16
+  const double* twf;  // [ds][4][32]  B fragments: {even freq, odd freq} x {even t, odd t}
+  const double* tw1;  // [2][ks1][32] B fragments of stage 2
+  const double2* tw0; // N0: (cos, sin)(2 pi j / N0)
+  const int4* umodes; // x = a index (0..N0-1), y = signed b, z = c
+  int n_umodes;
+  const long long* memb_u;
+  const int* shell_off;
+  int n_shells;
+  double factor;
+  int xc, chunks;     // planes per unit, units per field
+  double2* partial;   // [n_fields][chunks][n_umodes]
+  unsigned* ctrl;     // [0] unit counter, [1 + field] tickets (zeroed before the launch)
+  int work_doubles;   // size of the per-CTA scratch region
+  int ring_slots;     // TMA-ring variant: slots of 8 rows (power of two)
+  int slots_shift, groups_shift, xc_shift;  // log2 of ring_slots, N1 / 8, xc
+  double* shell_I;
+  int do_peaks;
+  const double* q;
+  PeakParams pp;
+  double* plot_y;
+  int32_t* peak_idx;
+  int32_t* n_peaks;
+};
+
+__host__ __device__ inline size_t fused_work_doubles(int N1, int n_shells, int n_umodes, int step, bool peaks) {
+  const size_t a = (size_t)16 * (N1 + 4) + 512;
+  const size_t b = (size_t)n_shells + n_umodes + 2 + (peaks ? peaks_smem_doubles(n_shells, step) : 0);
+  return a > b ? a : b;
+}
+__host__ __device__ inline size_t fused_smem_bytes(int N0, int N1, int N2, size_t work_doubles) {
+  return ((size_t)(N2 / 16) * 128 + 2 * (size_t)(N1 / 4) * 32 + 2 * (size_t)N0 + work_doubles) * sizeof(double);
+}
+
+// shell sums + peak search of one finished field; `work` = per-CTA scratch (fused_work_doubles)
+__device__ inline void fused_finish(const FusedArgs& A, int field, double* work) {
+  double* row = work;              // n_shells
+  double* Iu = work + A.n_shells;  // n_umodes (region reused by the peak search afterwards)
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
+  const double2* part = A.partial + (long long)field * A.chunks * A.n_umodes;
+  for (int u = tid; u < A.n_umodes; u += blockDim.x) {
+    double sr = 0.0, si = 0.0;
+    for (int ch = 0; ch < A.chunks; ++ch) {  // fixed order: independent of which CTA produced which unit
+      const double2 p = __ldcg(part + (long long)ch * A.n_umodes + u);
+      sr += p.x;
+      si += p.y;
+    }
+    Iu[u] = A.factor * (sr * sr + si * si);
+  }
+  __syncthreads();
+  for (int s = warp; s < A.n_shells; s += nwarp) {
+    double acc = 0.0;
+    for (int m = A.shell_off[s] + lane; m < A.shell_off[s + 1]; m += 32) acc += Iu[A.memb_u[m]];
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) acc += __shfl_xor_sync(0xffffffffu, acc, o);
+    if (lane == 0) {
+      row[s] = acc;
+      A.shell_I[(long long)field * A.n_shells + s] = acc;
+    }
+  }
+  if (!A.do_peaks) return;
+  __syncthreads();
+  peaks_block(A.q, row, A.n_shells, A.pp, A.plot_y ? A.plot_y + (long long)field * A.pp.step : nullptr,
+              A.peak_idx ? A.peak_idx + (long long)field * A.pp.max_peaks : nullptr,
+              A.n_peaks ? A.n_peaks + field : nullptr, work + A.n_shells);
+}
+
+__global__ void __launch_bounds__(256, 3)
+pruned_fused_kernel(const FusedArgs A) {
+  extern __shared__ double sm[];
+  double* twf = sm;                                   // ds * 128
+  double* tw1 = twf + (size_t)A.ds * 128;             // 2 * ks1 * 32
+  double2* tw0 = reinterpret_cast<double2*>(tw1 + (size_t)2 * A.ks1 * 32);  // N0
+  double* work = reinterpret_cast<double*>(tw0 + A.N0);
+  double* gT = work;                                  // 16 * gstride
+  double* c2 = gT + (size_t)16 * A.gstride;           // 256
+  double* hp = c2 + 256;                              // 256
+  __shared__ int s_unit, s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < A.ds * 128; i += 256) twf[i] = A.twf[i];
+  for (int i = tid; i < 2 * A.ks1 * 32; i += 256) tw1[i] = A.tw1[i];
+  for (int i = tid; i < A.N0; i += 256) tw0[i] = A.tw0[i];
+
+  // this thread's listed modes
+  int4 md[kFusedModesPerThread];
+  int orc[kFusedModesPerThread];
+#pragma unroll
+  for (int k = 0; k < kFusedModesPerThread; ++k) {
+    const int u = tid + 256 * k;
+    md[k] = u < A.n_umodes ? A.umodes[u] : make_int4(0, 0, 0, 0);
+    orc[k] = md[k].z * 16 + (md[k].y < 0 ? -md[k].y : md[k].y);
+  }
+  const int m = lane >> 2, kk = lane & 3;
+  const int groups = A.N1 >> 3;
+  const int n_units = A.n_fields * A.chunks;
+  const long long plane_doubles = (long long)A.N1 * A.N2;
+  // gT rows of this lane's accumulator columns n = 2 kk, 2 kk + 1 (even-frequency tile; odd tile = +1)
+  const int n0 = 2 * kk, n1 = 2 * kk + 1;
+  const int re0 = n0 < 4 ? 2 * n0 : 8 + 2 * (n0 - 4), re1 = n1 < 4 ? 2 * n1 : 8 + 2 * (n1 - 4);
+  __syncthreads();
+
+  for (;;) {
+    if (tid == 0) s_unit = (int)atomicAdd(&A.ctrl[0], 1u);
+    __syncthreads();
+    const int unit = s_unit;
+    if (unit >= n_units) break;
+    const int field = unit / A.chunks, chunk = unit - field * A.chunks;
+    const int x0 = chunk * A.xc;
+    double fr[kFusedModesPerThread], fi[kFusedModesPerThread];
+    int jj[kFusedModesPerThread];
+#pragma unroll
+    for (int k = 0; k < kFusedModesPerThread; ++k) {
+      fr[k] = 0.0; fi[k] = 0.0;
+      jj[k] = (int)(((long long)md[k].x * x0) % A.N0);
+    }
+    for (int x = x0; x < x0 + A.xc; ++x) {
+      const double* base = A.fields + ((long long)field * A.N0 + x) * plane_doubles;
+      // ---- stage 1 (z, folded): each warp transforms 8 rows at a time
+      for (int grp = warp; grp < groups; grp += 8) {
+        const double2* row = reinterpret_cast<const double2*>(base + (long long)(grp * 8 + m) * A.N2) + kk;
+        const double2* row2 = row + (A.N2 >> 2);
+        double e0 = 0.0, e1 = 0.0, o0 = 0.0, o1 = 0.0;
+#pragma unroll 4
+        for (int s = 0; s < A.ds; ++s) {
+          const double2 a = __ldg(row + 4 * s), b = __ldg(row2 + 4 * s);  // z = 8 s + 2 kk (+1), and + N2/2
+          const double* tw = twf + s * 128 + lane;
+          dmma_m8n8k4(e0, e1, a.x + b.x, tw[0]);
+          dmma_m8n8k4(e0, e1, a.y + b.y, tw[32]);
+          dmma_m8n8k4(o0, o1, a.x - b.x, tw[64]);
+          dmma_m8n8k4(o0, o1, a.y - b.y, tw[96]);
+        }
+        const int y = grp * 8 + m;
+        gT[(size_t)re0 * A.gstride + y] = e0;
+        gT[(size_t)re1 * A.gstride + y] = e1;
+        gT[(size_t)(re0 + 1) * A.gstride + y] = o0;
+        gT[(size_t)(re1 + 1) * A.gstride + y] = o1;
+      }
+      __syncthreads();
+      // ---- stage 2 (y): 16 x 16 x N1 product, 4 output tiles x 2 K halves over the 8 warps
+      {
+        const int mt = warp & 1, nt = (warp >> 1) & 1, kh = warp >> 2;
+        const int s0 = kh * (A.ks1 >> 1), s1 = s0 + (A.ks1 >> 1);
+        const double* arow = gT + (size_t)(8 * mt + m) * A.gstride;
+        const double* brow = tw1 + (size_t)nt * A.ks1 * 32;
+        double d0 = 0.0, d1 = 0.0;
+#pragma unroll 4
+        for (int s = s0; s < s1; ++s) dmma_m8n8k4(d0, d1, arow[4 * s + kk], brow[s * 32 + lane]);
+        const int r = 8 * mt + m, c = 8 * nt + 2 * kk;
+        if (kh == 1) { c2[r * 16 + c] = d0; c2[r * 16 + c + 1] = d1; }
+        __syncthreads();
+        if (kh == 0) { hp[r * 16 + c] = d0 + c2[r * 16 + c]; hp[r * 16 + c + 1] = d1 + c2[r * 16 + c + 1]; }
+      }
+      __syncthreads();
+      // ---- stage 3 (x): one thread per listed mode accumulates H[x,b,c] e^{-2 pi i a x / N0}
+#pragma unroll
+      for (int k = 0; k < kFusedModesPerThread; ++k) {
+        if (tid + 256 * k < A.n_umodes) {
+          const double rc = hp[orc[k]], rs = hp[orc[k] + 8], sc = hp[orc[k] + 128], ss = hp[orc[k] + 136];
+          const double hr = md[k].y >= 0 ? rc - ss : rc + ss;
+          const double hi = md[k].y >= 0 ? -(rs + sc) : rs - sc;
+          const double2 w = tw0[jj[k]];
+          fr[k] += hr * w.x + hi * w.y;
+          fi[k] += hi * w.x - hr * w.y;
+          jj[k] += md[k].x;
+          if (jj[k] >= A.N0) jj[k] -= A.N0;
+        }
+      }
+      // hp is rewritten only after the next plane's stage-1 barrier; gT after this plane's stage 2
+    }
+    double2* part = A.partial + (long long)unit * A.n_umodes;
+#pragma unroll
+    for (int k = 0; k < kFusedModesPerThread; ++k)
+      if (tid + 256 * k < A.n_umodes) part[tid + 256 * k] = make_double2(fr[k], fi[k]);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(&A.ctrl[1 + field], 1u) == (unsigned)(A.chunks - 1);
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      fused_finish(A, field, work);
+    }
+    __syncthreads();  // work / s_unit are reused by the next unit
+  }
+}
+
+// ------------------------------------------------------------------------------------------
+// TMA-ring variant (the default when it applies).  The LDG kernel above only has loads in flight while
+// a warp sits in its stage-1 loop; across the plane barriers and the y / x stages HBM idles.  Here one
+// persistent CTA of 16 warps per SM owns a ring of shared-memory slots, each holding a whole 8-row
+// group (8 N2 doubles, contiguous in the field) that arrives by ONE TMA bulk copy (cp.async.bulk +
+// mbarrier complete_tx; SASS UBLKCP).  Groups are numbered q = 0, 1, 2, ... through the CTA's whole
+// work (all planes of all its units); group q lives in slot q % S.  Warps take the next group number
+// from a shared counter, wait for its slot, transform it, and the same warp immediately refills the
+// slot with group q + S -- which may belong to the next plane or the next unit (units come from an
+// atomic counter, fetched two ahead) -- so ~180 KB per SM are in flight whatever the CTA is doing
+// (plane barriers, y / x stages, a field's finish).  Stage-2 twiddles are read through L1 to leave the
+// shared memory to the ring.  Requires N2 % 16 == 0, N1 % 8 == 0, at most 512 listed modes.
+// ------------------------------------------------------------------------------------------
+__device__ __forceinline__ uint32_t pf_smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+__device__ __forceinline__ void pf_mbar_init(uint64_t* bar, int count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(pf_smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void pf_mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(pf_smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void pf_bulk_g2s(void* dst, const void* src, uint32_t bytes, uint64_t* bar) {
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];" ::"r"(
+                   pf_smem_u32(dst)),
+               "l"(src), "r"(bytes), "r"(pf_smem_u32(bar))
+               : "memory");
+}
+__device__ __forceinline__ void pf_mbar_wait(uint64_t* bar, uint32_t parity) {
+  asm volatile(
+      "{\n"
+      ".reg .pred p;\n"
+      "PF_WAIT:\n"
+      "mbarrier.try_wait.parity.shared::cta.b64 p, [%0], %1;\n"
+      "@p bra PF_DONE;\n"
+      "bra PF_WAIT;\n"
+      "PF_DONE:\n"
+      "}\n" ::"r"(pf_smem_u32(bar)),
+      "r"(parity)
+      : "memory");
+}
+
+
+constexpr int kRingThreads = 512;   // 16 warps, one CTA per SM
+constexpr int kRingMaxSlots = 64;
+
+__host__ __device__ inline size_t ring_slot_bytes(int N2) { return (size_t)8 * N2 * 8; }
+__host__ __device__ inline size_t ring_work_doubles(int N1, int n_shells, int n_umodes, int step, bool peaks) {
+  const size_t a = (size_t)16 * (N1 + 4) + 1024;  // gT | c2 (3 x 256) | hp (256)
+  const size_t b = (size_t)n_shells + n_umodes + 2 + (peaks ? peaks_smem_doubles(n_shells, step) : 0);
+  return a > b ? a : b;
+}
+__host__ __device__ inline size_t ring_fixed_bytes(int N0, int N2, size_t work_doubles) {
+  return ((size_t)(N2 / 16) * 128 + 2 * (size_t)N0 + work_doubles) * sizeof(double) + kRingMaxSlots * 8;
+}
+
+__global__ void __launch_bounds__(kRingThreads, 1)
+pruned_ring_kernel(const FusedArgs A) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  const int S = A.ring_slots;
+  const size_t slot_bytes = ring_slot_bytes(A.N2);
+  unsigned char* ring = smraw;
+  uint64_t* full = reinterpret_cast<uint64_t*>(ring + (size_t)S * slot_bytes);
+  double* twf = reinterpret_cast<double*>(full + kRingMaxSlots);          // ds * 128
+  double2* tw0 = reinterpret_cast<double2*>(twf + (size_t)A.ds * 128);    // N0
+  double* work = reinterpret_cast<double*>(tw0 + A.N0);
+  double* gT = work;                                  // 16 * gstride
+  double* c2 = gT + (size_t)16 * A.gstride;           // 3 * 256
+  double* hp = c2 + 768;                              // 256
+  __shared__ int s_units[4];
+  __shared__ const double* s_ubase[4];
+  __shared__ int s_q, s_last;
+  __shared__ volatile int s_issued[kRingMaxSlots];  // how many times each slot has been requested
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  if (tid < kRingMaxSlots) s_issued[tid] = 0;
+  for (int i = tid; i < A.ds * 128; i += kRingThreads) twf[i] = A.twf[i];
+  for (int i = tid; i < A.N0; i += kRingThreads) tw0[i] = A.tw0[i];
+  if (tid < S) pf_mbar_init(&full[tid], 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  // first plane of unit u (nullptr past the end), so that a refill needs no division
+  auto unit_base = [&](int u) -> const double* {
+    if (u >= A.n_fields * A.chunks) return nullptr;
+    const int f = u / A.chunks, ch = u - f * A.chunks;
+    return A.fields + ((long long)f * A.N0 + (long long)ch * A.xc) * ((long long)A.N1 * A.N2);
+  };
+  if (tid == 0) {
+    s_units[0] = (int)atomicAdd(&A.ctrl[0], 1u);
+    s_units[1] = (int)atomicAdd(&A.ctrl[0], 1u);
+    s_ubase[0] = unit_base(s_units[0]);
+    s_ubase[1] = unit_base(s_units[1]);
+    s_q = 16;  // group numbers 0..15 start out with warps 0..15
+  }
+  // this thread's listed mode
+  const int4 md = tid < A.n_umodes ? A.umodes[tid] : make_int4(0, 0, 0, 0);
+  const int orc = md.z * 16 + (md.y < 0 ? -md.y : md.y);
+  const int m = lane >> 2, kk = lane & 3;
+  const int groups = A.N1 >> 3;
+  const int n_units = A.n_fields * A.chunks;
+  const long long plane_doubles = (long long)A.N1 * A.N2;
+  const int n0 = 2 * kk, n1 = 2 * kk + 1;
+  const int re0 = n0 < 4 ? 2 * n0 : 8 + 2 * (n0 - 4), re1 = n1 < 4 ? 2 * n1 : 8 + 2 * (n1 - 4);
+  __syncthreads();
+
+  // lane 0: request group q (CTA-local numbering) into its slot; nothing to do past the last unit.
+  // groups per plane, planes per unit and ring slots are powers of two: shifts, no integer division.
+  const int g_sh = A.groups_shift, x_sh = A.xc_shift, s_mask = S - 1, s_sh = A.slots_shift;
+  auto issue = [&](int q) {
+    if (lane == 0) {
+      const int pn = q >> g_sh, g = q & (groups - 1);
+      const int kn = pn >> x_sh, xi = pn & (A.xc - 1);
+      const double* ubase = s_ubase[kn & 3];
+      if (ubase) {
+        const double* rows = ubase + (long long)xi * plane_doubles + (long long)g * 8 * A.N2;
+        const int sl = q & s_mask;
+        pf_mbar_expect_tx(&full[sl], (uint32_t)slot_bytes);
+        pf_bulk_g2s(ring + (size_t)sl * slot_bytes, rows, (uint32_t)slot_bytes, &full[sl]);
+        __threadfence_block();
+        s_issued[sl] = (q >> s_sh) + 1;
+      }
+    }
+  };
+  for (int q = warp; q < S; q += 16) issue(q);
+  int myq = warp;
+
+  for (int k = 0;; ++k) {
+    const int unit = s_units[k & 3];
+    if (unit >= n_units) break;
+    if (tid == 0) {  // read (after barriers) from unit k+1 on
+      const int u2 = (int)atomicAdd(&A.ctrl[0], 1u);
+      s_units[(k + 2) & 3] = u2;
+      s_ubase[(k + 2) & 3] = unit_base(u2);
+    }
+    const int field = unit / A.chunks, chunk = unit - field * A.chunks;
+    const int x0 = chunk * A.xc;
+    double fr = 0.0, fi = 0.0;
+    int jj = (int)(((long long)md.x * x0) % A.N0);
+    for (int xi = 0; xi < A.xc; ++xi) {
+      const int plane_start = (k * A.xc + xi) * groups, plane_end = plane_start + groups;
+      // ---- stage 1 (z, folded): warps take group numbers until the plane is used up
+      while (myq < plane_end) {
+        const int sl = myq & s_mask, use = myq >> s_sh;
+        // a parity wait is only meaningful once the slot's previous use is over: wait until this use has been
+        // requested (which happens after the previous group was consumed), then for its bytes
+        if (lane == 0) while (s_issued[sl] <= use) {}
+        __syncwarp();
+        pf_mbar_wait(&full[sl], (uint32_t)use & 1u);
+        const unsigned char* slot = ring + (size_t)sl * slot_bytes;
+        const double2* ra = reinterpret_cast<const double2*>(slot + (size_t)m * A.N2 * 8) + kk;
+        const double2* rb = ra + (A.N2 >> 2);
+        double e0 = 0.0, e1 = 0.0, o0 = 0.0, o1 = 0.0;
+#pragma unroll 4
+        for (int s = 0; s < A.ds; ++s) {
+          const double2 a = ra[4 * s], b = rb[4 * s];
+          const double* tw = twf + s * 128 + lane;
+          dmma_m8n8k4(e0, e1, a.x + b.x, tw[0]);
+          dmma_m8n8k4(e0, e1, a.y + b.y, tw[32]);
+          dmma_m8n8k4(o0, o1, a.x - b.x, tw[64]);
+          dmma_m8n8k4(o0, o1, a.y - b.y, tw[96]);
+        }
+        __syncwarp();
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        issue(myq + S);
+        const int y = (myq - plane_start) * 8 + m;
+        gT[(size_t)re0 * A.gstride + y] = e0;
+        gT[(size_t)re1 * A.gstride + y] = e1;
+        gT[(size_t)(re0 + 1) * A.gstride + y] = o0;
+        gT[(size_t)(re1 + 1) * A.gstride + y] = o1;
+        int nq = 0;
+        if (lane == 0) nq = atomicAdd(&s_q, 1);
+        myq = __shfl_sync(0xffffffffu, nq, 0);
+      }
+      __syncthreads();
+      // ---- stage 2 (y): 16 x 16 x N1 product, 4 output tiles x 4 K quarters over the 16 warps
+      {
+        const int mt = warp & 1, nt = (warp >> 1) & 1, kh = warp >> 2;
+        const int s0 = kh * (A.ks1 >> 2), s1 = s0 + (A.ks1 >> 2);
+        const double* arow = gT + (size_t)(8 * mt + m) * A.gstride;
+        const double* brow = A.tw1 + (size_t)nt * A.ks1 * 32;
+        double d0 = 0.0, d1 = 0.0;
+#pragma unroll 4
+        for (int s = s0; s < s1; ++s) dmma_m8n8k4(d0, d1, arow[4 * s + kk], __ldg(brow + s * 32 + lane));
+        const int r = 8 * mt + m, c = 8 * nt + 2 * kk;
+        if (kh > 0) { c2[(kh - 1) * 256 + r * 16 + c] = d0; c2[(kh - 1) * 256 + r * 16 + c + 1] = d1; }
+        __syncthreads();
+        if (kh == 0) {
+          hp[r * 16 + c] = ((d0 + c2[r * 16 + c]) + c2[256 + r * 16 + c]) + c2[512 + r * 16 + c];
+          hp[r * 16 + c + 1] = ((d1 + c2[r * 16 + c + 1]) + c2[256 + r * 16 + c + 1]) + c2[512 + r * 16 + c + 1];
+        }
+      }
+      __syncthreads();
+      // ---- stage 3 (x): one thread per listed mode
+      if (tid < A.n_umodes) {
+        const double rc = hp[orc], rs = hp[orc + 8], sc = hp[orc + 128], ss = hp[orc + 136];
+        const double hr = md.y >= 0 ? rc - ss : rc + ss;
+        const double hi = md.y >= 0 ? -(rs + sc) : rs - sc;
+        const double2 w = tw0[jj];
+        fr += hr * w.x + hi * w.y;
+        fi += hi * w.x - hr * w.y;
+        jj += md.x;
+        if (jj >= A.N0) jj -= A.N0;
+      }
+    }
+    if (tid < A.n_umodes) A.partial[(long long)unit * A.n_umodes + tid] = make_double2(fr, fi);
+    __threadfence();
+    __syncthreads();
+    if (tid == 0) s_last = atomicAdd(&A.ctrl[1 + field], 1u) == (unsigned)(A.chunks - 1);
+    __syncthreads();
+    if (s_last) {
+      __threadfence();
+      fused_finish(A, field, work);
+    }
+    __syncthreads();
+  }
+}
+
+}  // namespace sbx

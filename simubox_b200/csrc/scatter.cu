@@ -14,6 +14,7 @@
 #include "common.h"
 #include "pruned_dft.cuh"
 #include "scatter_kernels.cuh"
+#include "pruned_fused.cuh"
 #include "shell_table.h"
 
 namespace sbx {
@@ -99,6 +100,12 @@ struct sbx_scatter_plan {
   double* d_planes = nullptr;
   int n_umodes = 0;
   bool pruned_ok = false;
+  // fused single-kernel variant (pruned_fused.cuh)
+  bool fused_ok = false;
+  double* d_twf = nullptr;
+  double2* d_partial = nullptr;
+  unsigned* d_ctrl = nullptr;
+  int fused_xc = 1;
   cudaStream_t s_aux = nullptr;
   cudaEvent_t ev_planes[2] = {nullptr, nullptr}, ev_finish[2] = {nullptr, nullptr};
   std::map<int, cufftHandle> fft;  // batch -> plan
@@ -283,6 +290,29 @@ static int build_pruned_tables(sbx_scatter_plan* p) {
   }
   if (const char* e = getenv("SBX_PRUNED_VARIANT")) p->pruned_variant = (atoi(e) == 1 && p->d_tw2f) ? 1 : 0;
   if (const char* e = getenv("SBX_PRUNED_CTAS")) p->pruned_ctas_per_sm = std::max(1, std::min(3, atoi(e)));
+  if (N2 % 16 == 0 && N1 % 8 == 0 && umodes.size() <= (size_t)256 * kFusedModesPerThread) {
+    // fold fragments (pruned_fused.cuh): step s covers z = 8 s .. 8 s + 7 of both halves of a row
+    const int64_t ds = N2 / 16;
+    std::vector<double> twf((size_t)ds * 128);
+    for (int64_t s = 0; s < ds; ++s)
+      for (int lane = 0; lane < 32; ++lane) {
+        const int64_t k = lane & 3, n = lane >> 2, te = 8 * s + 2 * k, to = te + 1;
+        const int64_t ce = n < 4 ? 2 * n : 2 * (n - 4), co = ce + 1;  // even / odd frequency of column n
+        const bool is_cos = n < 4;
+        twf[(size_t)s * 128 + lane] = is_cos ? cos2pi(ce * te, N2) : sin2pi(ce * te, N2);
+        twf[(size_t)s * 128 + 32 + lane] = is_cos ? cos2pi(ce * to, N2) : sin2pi(ce * to, N2);
+        twf[(size_t)s * 128 + 64 + lane] = is_cos ? cos2pi(co * te, N2) : sin2pi(co * te, N2);
+        twf[(size_t)s * 128 + 96 + lane] = is_cos ? cos2pi(co * to, N2) : sin2pi(co * to, N2);
+      }
+    if ((rc = upload(&p->d_twf, twf))) return rc;
+    p->fused_xc = N0 % 4 == 0 ? 4 : (N0 % 2 == 0 ? 2 : 1);
+    if (const char* e = getenv("SBX_FUSED_XC")) {
+      const int v = atoi(e);
+      if (v >= 1 && N0 % v == 0) p->fused_xc = v;
+    }
+    const size_t work = fused_work_doubles((int)N1, t.n_shells(), (int)umodes.size(), 2000, true);
+    p->fused_ok = fused_smem_bytes((int)N0, (int)N1, (int)N2, work) <= 200 * 1024;
+  }
   if ((rc = upload(&p->d_tw0, tw0))) return rc;
   if ((rc = upload(&p->d_umodes, umodes))) return rc;
   if ((rc = upload(&p->d_memb_u, memb))) return rc;
@@ -320,6 +350,7 @@ static void free_plan(sbx_scatter_plan* p) {
   cudaFree(p->d_spec);
   cudaFree(p->d_tw2); cudaFree(p->d_tw2f); cudaFree(p->d_tw1); cudaFree(p->d_tw0); cudaFree(p->d_umodes); cudaFree(p->d_memb_u);
   cudaFree(p->d_planes);
+  cudaFree(p->d_twf); cudaFree(p->d_partial); cudaFree(p->d_ctrl);
   for (int i = 0; i < 2; ++i) {
     cudaFree(p->d_stage[i]); cudaFree(p->d_out[i]); cudaFree(p->d_pidx[i]); cudaFree(p->d_npk[i]);
     if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
@@ -337,6 +368,7 @@ static void free_plan(sbx_scatter_plan* p) {
 }
 
 static const size_t kMaxDynSmem = 200 * 1024;
+static const size_t kMaxTmaSmem = 226 * 1024;
 
 extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, int ndim, const int64_t* N,
                                           const double* L, int cutoff, double threshold, int max_batch,
@@ -370,14 +402,19 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   const GridDev& g = p->grid;
   if ((rc = build_pruned_tables(p))) { free_plan(p); return rc; }
   if (path == SBX_SCATTER_AUTO) {
-    if (p->pruned_ok && !getenv("SBX_NO_PRUNED")) path = SBX_SCATTER_PRUNED;
+    if (p->pruned_ok && p->fused_ok && !getenv("SBX_NO_PRUNED") && !getenv("SBX_NO_FUSED")) path = SBX_SCATTER_PRUNED_FUSED;
+    else if (p->pruned_ok && !getenv("SBX_NO_PRUNED")) path = SBX_SCATTER_PRUNED;
     else path = (p->tab.n_members() * 4 <= g.nspec) ? SBX_SCATTER_FFT_GATHER : SBX_SCATTER_FFT_DENSE;
   }
   if (path == SBX_SCATTER_PRUNED && !p->pruned_ok) {
     free_plan(p);
     return fail(SBX_EINVAL, "pruned-DFT path needs a 3D grid (N1 %% 8 == 0, N1,N2 >= 16) whose shell modes have |k_y|,k_z <= 7");
   }
-  if (path != SBX_SCATTER_FFT_DENSE && path != SBX_SCATTER_FFT_GATHER && path != SBX_SCATTER_PRUNED) {
+  if (path == SBX_SCATTER_PRUNED_FUSED && !(p->pruned_ok && p->fused_ok)) {
+    free_plan(p);
+    return fail(SBX_EINVAL, "fused pruned-DFT path needs the pruned path's conditions plus N2 %% 16 == 0 and at most %d listed modes", 256 * kFusedModesPerThread);
+  }
+  if (path != SBX_SCATTER_FFT_DENSE && path != SBX_SCATTER_FFT_GATHER && path != SBX_SCATTER_PRUNED && path != SBX_SCATTER_PRUNED_FUSED) {
     free_plan(p);
     return fail(SBX_EINVAL, "unknown scatter path %d", path);
   }
@@ -395,7 +432,7 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   if (path == SBX_SCATTER_FFT_GATHER) chunk = (size_t)max_batch;  // one CTA per field: launch many fields at once
   if (const char* e = getenv("SBX_FFT_CHUNK")) chunk = std::max(1, atoi(e));
   p->chunk = (int)std::min<size_t>(chunk, (size_t)max_batch);
-  if (path == SBX_SCATTER_PRUNED) p->chunk = max_batch;
+  if (path == SBX_SCATTER_PRUNED || path == SBX_SCATTER_PRUNED_FUSED) p->chunk = max_batch;
   const long long want = (4LL * p->sm_count + p->chunk - 1) / p->chunk;
   long long bpf = std::max<long long>((g.nspec + 16383) / 16384, want);
   bpf = std::min<long long>(bpf, std::max<long long>(1, g.nspec / 256));
@@ -410,6 +447,11 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
       if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_finish[i], cudaEventDisableTiming);
     }
   }
+  else if (path == SBX_SCATTER_PRUNED_FUSED) {
+    const size_t chunks = (size_t)g.N0 / p->fused_xc;
+    e = cudaMalloc((void**)&p->d_partial, (size_t)p->chunk * chunks * std::max(p->n_umodes, 1) * sizeof(double2));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_ctrl, ((size_t)p->chunk + 1) * sizeof(unsigned));
+  }
   else e = cudaMalloc((void**)&p->d_spec, (size_t)p->chunk * g.nspec * sizeof(double2));
   if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_tickets, (size_t)max_batch * sizeof(unsigned));
   if (e == cudaSuccess) e = cudaMemset(p->d_tickets, 0, (size_t)max_batch * sizeof(unsigned));
@@ -418,10 +460,12 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
     return fail(e == cudaErrorMemoryAllocation ? SBX_ENOMEM : SBX_ECUDA, "plan allocation: %s", cudaGetErrorString(e));
   }
   cufftHandle h;
-  if (path != SBX_SCATTER_PRUNED && (rc = get_fft(p, p->chunk, &h))) { free_plan(p); return rc; }
+  if (path != SBX_SCATTER_PRUNED && path != SBX_SCATTER_PRUNED_FUSED && (rc = get_fft(p, p->chunk, &h))) { free_plan(p); return rc; }
   cudaFuncSetAttribute(pruned_planes_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_planes_fullk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(pruned_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(pruned_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
@@ -496,6 +540,60 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
   int rc;
   if (do_peaks && (rc = check_peaks_args(ns, pp.step, pp.max_peaks))) return rc;
   const size_t smem_peaks = do_peaks ? (peaks_smem_doubles(ns, pp.step) + ns) * sizeof(double) : 0;
+  if (p->path == SBX_SCATTER_PRUNED_FUSED) {
+    FusedArgs A{};
+    A.N0 = g.N0; A.N1 = g.N1; A.N2 = g.N2;
+    A.ks1 = g.N1 / 4; A.gstride = g.N1 + 4; A.ds = g.N2 / 16;
+    A.twf = p->d_twf; A.tw1 = p->d_tw1; A.tw0 = p->d_tw0;
+    A.umodes = p->d_umodes; A.n_umodes = p->n_umodes; A.memb_u = p->d_memb_u; A.shell_off = p->d_shell_off;
+    A.n_shells = ns; A.factor = g.factor;
+    A.xc = p->fused_xc; A.chunks = g.N0 / p->fused_xc;
+    A.partial = p->d_partial; A.ctrl = p->d_ctrl;
+    A.do_peaks = do_peaks ? 1 : 0; A.q = p->d_q; A.pp = pp;
+    const size_t work = fused_work_doubles(g.N1, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks);
+    A.work_doubles = (int)work;
+    const size_t smem = fused_smem_bytes(g.N0, g.N1, g.N2, work);
+    if (smem > kMaxDynSmem) return fail(SBX_EINVAL, "fused pruned kernel needs %zu bytes of shared memory", smem);
+    // TMA-ring variant when the grid allows it and a useful ring fits in shared memory
+    static const int tma_on = [] { const char* e = getenv("SBX_FUSED_TMA"); return e ? atoi(e) : 1; }();
+    const size_t rwork = ring_work_doubles(g.N1, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks);
+    const size_t rfixed = ring_fixed_bytes(g.N0, g.N2, rwork);
+    int slots = rfixed < kMaxTmaSmem ? (int)((kMaxTmaSmem - rfixed) / ring_slot_bytes(g.N2)) : 0;
+    slots = std::min(slots, std::min(kRingMaxSlots, A.xc * (g.N1 / 8)));  // refills look at most one unit ahead
+    if (const char* e = getenv("SBX_RING_SLOTS")) slots = std::min(slots, std::max(1, atoi(e)));
+    auto ilog2 = [](int v) { int l = 0; while ((1 << (l + 1)) <= v) ++l; return l; };
+    auto pow2 = [](int v) { return v > 0 && (v & (v - 1)) == 0; };
+    slots = slots > 0 ? 1 << ilog2(slots) : 0;  // power of two: slot = q & (S - 1)
+    const bool use_tma = tma_on && g.N1 % 16 == 0 && pow2(g.N1 / 8) && pow2(A.xc) && p->n_umodes <= kRingThreads && slots >= 4;
+    A.slots_shift = slots > 0 ? ilog2(slots) : 0;
+    A.groups_shift = ilog2(g.N1 / 8);
+    A.xc_shift = ilog2(A.xc);
+    const size_t smem_tma = rfixed + (size_t)slots * ring_slot_bytes(g.N2);
+    A.ring_slots = slots;
+    if (use_tma) A.work_doubles = (int)rwork;
+    for (int c0 = 0; c0 < batch; c0 += p->chunk) {
+      const int nb = std::min(p->chunk, batch - c0);
+      A.fields = fields + (size_t)c0 * g.nreal;
+      A.n_fields = nb;
+      A.shell_I = shell_I + (size_t)c0 * ns;
+      A.plot_y = plot_y ? plot_y + (size_t)c0 * pp.step : nullptr;
+      A.peak_idx = peak_idx ? peak_idx + (size_t)c0 * pp.max_peaks : nullptr;
+      A.n_peaks = n_peaks ? n_peaks + c0 : nullptr;
+      SBX_CUDA(cudaMemsetAsync(p->d_ctrl, 0, ((size_t)nb + 1) * sizeof(unsigned), st));
+      const long long units = (long long)nb * A.chunks;
+      const int grid1 = (int)std::min<long long>(units, (long long)p->pruned_ctas_per_sm * p->sm_count);
+      if (p->profiling) prof_event(p, st);
+      if (use_tma) {
+        const int grid2 = (int)std::min<long long>(units, (long long)p->sm_count);
+        pruned_ring_kernel<<<grid2, kRingThreads, smem_tma, st>>>(A);
+      } else
+      pruned_fused_kernel<<<grid1, 256, smem, st>>>(A);
+      SBX_CUDA(cudaGetLastError());
+      if (p->profiling) { prof_event(p, st); prof_event(p, st); }
+      p->own_launches += 1;
+    }
+    return SBX_OK;
+  }
   if (p->path == SBX_SCATTER_PRUNED) {
     const size_t sm1 = p->pruned_variant == 1 ? pruned_fullk_smem_bytes(g.N1, g.N2) : pruned_smem_bytes(g.N1, g.N2);
     const size_t need2 = ((size_t)p->n_umodes + 2 + 2 * (size_t)g.N0) * sizeof(double);

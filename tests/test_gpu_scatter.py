@@ -13,7 +13,7 @@ from test_oracle_golden import last_shell_members
 
 pytestmark = pytest.mark.gpu
 
-DENSE, GATHER, PRUNED = 1, 2, 3
+DENSE, GATHER, PRUNED, FUSED = 1, 2, 3, 4
 
 
 @pytest.fixture(scope="module")
@@ -33,14 +33,14 @@ def run_scatter(sbx_lib, torch, mats, L, cutoff, thr, path, peaks=None):
     try:
         out = Scatter.sacttering_peak_batch(fields, L, cutoff=cutoff, threshold=thr, path=path, max_batch=len(mats), **kw)
     except sbx_lib.SbxError as e:
-        if path == PRUNED and e.code == -1:
+        if path in (PRUNED, FUSED) and e.code == -1:
             pytest.skip("pruned-DFT path not applicable to this grid / cutoff")
         raise
     torch.cuda.synchronize()
     return out
 
 
-@pytest.mark.parametrize("path", [DENSE, GATHER, PRUNED])
+@pytest.mark.parametrize("path", [DENSE, GATHER, PRUNED, FUSED])
 @pytest.mark.parametrize("name", golden_names("scatter_"))
 def test_scatter_matches_reference_golden(sbx_lib, torch_cuda, name, path):
     g = golden(name)
@@ -55,7 +55,7 @@ def test_fused_peaks_match_reference_golden(sbx_lib, torch_cuda, name):
     g = golden(name)
     kw = json.loads(str(g["peak_kw"]))
     mat, L, cutoff, thr = golden_field(g), g["L"], int(g["cutoff"]), float(g["threshold"])
-    paths = [DENSE, GATHER] + ([PRUNED] if "synth" in name else [])
+    paths = [DENSE, GATHER] + ([PRUNED, FUSED] if "synth" in name else [])
     for path in paths:
         out = run_scatter(sbx_lib, torch_cuda, [mat, mat], L, cutoff, thr, path, peaks=kw)
         for b in range(2):
@@ -149,11 +149,14 @@ def test_properties_at_baseline_sizes(sbx_lib, torch_cuda, n, cells):
     L = synth.box_for(cells)
     f = synth.fields_torch(0, 2, (n, n, n), cells=cells)
     shifted = torch.roll(f, shifts=(5, n // 3, 1), dims=(1, 2, 3)).contiguous()
-    outs = {p: Scatter.sacttering_peak_batch(f, L, path=p, max_batch=2)["I"].cpu().numpy() for p in (DENSE, GATHER, PRUNED)}
+    outs = {p: Scatter.sacttering_peak_batch(f, L, path=p, max_batch=2)["I"].cpu().numpy() for p in (DENSE, GATHER, PRUNED, FUSED)}
     tol = 1e-9 * np.abs(outs[GATHER]) + 1e-12 * np.abs(outs[GATHER]).max()
     assert np.all(np.abs(outs[DENSE] - outs[GATHER]) <= tol)
     assert np.all(np.abs(outs[PRUNED] - outs[GATHER]) <= tol)
-    Ip = Scatter.sacttering_peak_batch(shifted, L, path=PRUNED, max_batch=2)["I"].cpu().numpy()
+    assert np.all(np.abs(outs[FUSED] - outs[GATHER]) <= tol)
+    again = Scatter.sacttering_peak_batch(f, L, path=FUSED, max_batch=1)["I"].cpu().numpy()
+    assert np.array_equal(again, outs[FUSED]), "fused path must be bitwise reproducible whatever the unit schedule"
+    Ip = Scatter.sacttering_peak_batch(shifted, L, path=FUSED, max_batch=2)["I"].cpu().numpy()
     assert np.all(np.abs(Ip[:, :-1] - outs[GATHER][:, :-1]) <= tol[:, :-1])
     I = outs[GATHER]
     dc = (f.sum(dim=(1, 2, 3)) ** 2 / n ** 3).cpu().numpy()
@@ -171,14 +174,16 @@ def test_properties_at_baseline_sizes(sbx_lib, torch_cuda, n, cells):
 
 @pytest.mark.parametrize("shape,L,cutoff", [((16, 16, 16), (4.0, 4.0, 4.0), 30), ((32, 24, 20), (8.0, 6.0, 5.0), 30),
                                             ((20, 32, 48), (3.0, 5.0, 7.0), 40), ((64, 64, 64), (8.0, 8.0, 8.0), 30),
-                                            ((18, 40, 22), (2.0, 9.0, 4.0), 12)])
-def test_pruned_dft_vs_oracle(sbx_lib, torch_cuda, shape, L, cutoff):
+                                            ((18, 40, 22), (2.0, 9.0, 4.0), 12), ((6, 16, 32), (2.0, 4.0, 8.0), 20),
+                                            ((10, 24, 16), (5.0, 6.0, 4.0), 30)])
+@pytest.mark.parametrize("path", [PRUNED, FUSED])
+def test_pruned_dft_vs_oracle(sbx_lib, torch_cuda, shape, L, cutoff, path):
     """Hand-written pruned DFT (DMMA stages + finish kernel) against the numpy oracle, incl. non-cubic grids
     where the meshgrid 'xy' pairing (quirk Q1) decides which modes are needed."""
     rng = np.random.default_rng(sum(shape))
     mats = [rng.standard_normal(shape) for _ in range(3)]
-    out = run_scatter(sbx_lib, torch_cuda, mats, L, cutoff, 1e-12, PRUNED, peaks=dict(width=0.5, step=500, cutoff=1e9, min_height=0.0))
-    assert out["path"] == "pruned_dft"
+    out = run_scatter(sbx_lib, torch_cuda, mats, L, cutoff, 1e-12, path, peaks=dict(width=0.5, step=500, cutoff=1e9, min_height=0.0))
+    assert out["path"] == ("pruned_dft" if path == PRUNED else "pruned_dft_fused")
     for b, mat in enumerate(mats):
         ref, _ = scatter_np.scattering_peak_table(mat, L, cutoff, 1e-12)
         qI = np.stack([out["q"], out["I"][b].cpu().numpy()], axis=1)
@@ -188,7 +193,8 @@ def test_pruned_dft_vs_oracle(sbx_lib, torch_cuda, shape, L, cutoff):
 def test_auto_path_selection(sbx_lib, torch_cuda):
     from simubox_b200.scatter import get_plan
 
-    assert get_plan((64, 64, 64), (8, 8, 8), 30, 1e-12).path == PRUNED          # few low modes: pruned DFT
+    assert get_plan((64, 64, 64), (8, 8, 8), 30, 1e-12).path == FUSED           # few low modes: fused pruned DFT
+    assert get_plan((40, 40, 40), (8, 8, 8), 30, 1e-12).path == PRUNED          # N2 % 16 != 0: two-kernel pruned DFT
     assert get_plan((64, 64, 64), (8, 8, 8), 60, 1e-12).path == GATHER          # modes beyond the 8x8 tile: cuFFT + gather
     assert get_plan((16, 16, 16), (4, 4, 4), 10 ** 6, 1e-12).path == DENSE      # every mode binned: cuFFT + dense scan
     assert get_plan((192, 192), (6.2, 6.2), 300, 1e-12).path in (GATHER, DENSE)  # 2D: cuFFT paths
