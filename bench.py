@@ -279,7 +279,7 @@ def run_scatter(args):
     pipeline_bytes = 8 * n ** 3 + 2 * spec_bytes
     pathname = _lib.PATH_NAMES[plan.path]
     if plan.path == 4:  # fused pruned DFT: ONE kernel reads each field exactly once and finishes it
-        kern, unit_bytes = "pruned_fused_kernel", 8 * n ** 3
+        kern, unit_bytes = (plan.kernel or "pruned_fused_kernel"), 8 * n ** 3
         launches_per_step = own_per_step
         fused_ms_per_launch = prof["transform_ms"] / max(prof["own_launches"], 1)
     elif plan.path == 3:  # pruned DFT: pruned_planes_kernel reads each field exactly once (first event pair)
@@ -295,7 +295,7 @@ def run_scatter(args):
             "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
             "algorithmic_bytes_per_field": unit_bytes, "fields_per_launch": fields_per_launch,
             "kernel_ms_per_launch": fused_ms_per_launch,
-            "step_split_ms": ({"pruned_fused_kernel": transform_ms_per_step} if plan.path == 4 else
+            "step_split_ms": ({kern: transform_ms_per_step} if plan.path == 4 else
                               {"pruned_planes_kernel": transform_ms_per_step, "pruned_finish_kernel": fused_ms_per_step} if plan.path == 3
                               else {"transform(cuFFT)": transform_ms_per_step, "own_kernels": fused_ms_per_step}),
             "pipeline": {"bytes_per_field": pipeline_bytes, "achieved": pipeline_bytes * B / (ms * 1e-3) / 1e9,

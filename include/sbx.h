@@ -85,6 +85,8 @@ int sbx_scatter_plan_members(const sbx_scatter_plan* plan, int shell, int64_t* n
                              double* k2xyz_host, int64_t capacity);
 /* which SBX_SCATTER_* path the plan runs */
 int sbx_scatter_plan_path(const sbx_scatter_plan* plan);
+/* name of the dominant hand-written kernel the last execute launched ("" before the first one) */
+const char* sbx_scatter_plan_kernel(const sbx_scatter_plan* plan);
 
 /* Live profiling for bench.py: when enabled every chunk launch is bracketed by CUDA events on
  * the launching stream.  get_profile synchronises on the last event and returns the summed

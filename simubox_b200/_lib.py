@@ -33,6 +33,7 @@ _SIGNATURES = {
     "sbx_scatter_plan_shells": (C.c_int, [_vp, C.POINTER(C.c_int), _f64p, _i64p]),
     "sbx_scatter_plan_members": (C.c_int, [_vp, C.c_int, _i64p, _f64p, C.c_int64]),
     "sbx_scatter_plan_path": (C.c_int, [_vp]),
+    "sbx_scatter_plan_kernel": (C.c_char_p, [_vp]),
     "sbx_scatter_plan_set_profiling": (C.c_int, [_vp, C.c_int]),
     "sbx_scatter_plan_get_profile": (C.c_int, [_vp, _f64p, _f64p, _i64p, _i64p, C.c_int]),
     "sbx_scatter_execute": (C.c_int, [_vp, _vp, C.c_int, _vp, _vp]),
@@ -120,6 +121,11 @@ class ScatterPlan:
     @property
     def handle(self):
         return self._h
+
+    @property
+    def kernel(self) -> str:
+        """Dominant hand-written kernel of the last execute (empty before the first one)."""
+        return (lib().sbx_scatter_plan_kernel(self._h) or b"").decode()
 
     def members(self, shell: int) -> np.ndarray:
         """(n, ndim) squared-k component vectors of the modes in ``shell`` (= q_idx[shell])."""

@@ -102,6 +102,7 @@ struct sbx_scatter_plan {
   bool pruned_ok = false;
   // fused single-kernel variant (pruned_fused.cuh)
   bool fused_ok = false;
+  const char* last_kernel = "";  // dominant hand-written kernel of the last execute (bench roofline)
   double* d_twf = nullptr;
   double2* d_partial = nullptr;
   unsigned* d_ctrl = nullptr;
@@ -486,6 +487,7 @@ extern "C" int sbx_scatter_plan_destroy(sbx_scatter_plan* plan) {
 }
 
 extern "C" int sbx_scatter_plan_path(const sbx_scatter_plan* plan) { return plan ? plan->path : SBX_EINVAL; }
+extern "C" const char* sbx_scatter_plan_kernel(const sbx_scatter_plan* plan) { return plan ? plan->last_kernel : ""; }
 
 extern "C" int sbx_scatter_plan_shells(const sbx_scatter_plan* plan, int* n_shells, double* q_host,
                                        int64_t* count_host) {
@@ -564,7 +566,11 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
     auto ilog2 = [](int v) { int l = 0; while ((1 << (l + 1)) <= v) ++l; return l; };
     auto pow2 = [](int v) { return v > 0 && (v & (v - 1)) == 0; };
     slots = slots > 0 ? 1 << ilog2(slots) : 0;  // power of two: slot = q & (S - 1)
-    const bool use_tma = tma_on && g.N1 % 16 == 0 && pow2(g.N1 / 8) && pow2(A.xc) && p->n_umodes <= kRingThreads && slots >= 4;
+    // Measured on B200 (profiles/r01): the ring wins from 256^2 planes on (0.81 vs 0.98 ms per 32 x 256^3), the
+    // 3-CTA/SM LDG kernel on smaller planes (0.94 vs 1.06 ms per 256 x 128^3); SBX_FUSED_TMA=2 forces the ring.
+    const bool ring_fits = g.N1 % 16 == 0 && pow2(g.N1 / 8) && pow2(A.xc) && p->n_umodes <= kRingThreads && slots >= 4;
+    const bool use_tma = ring_fits && (tma_on >= 2 || (tma_on == 1 && (long long)g.N1 * g.N2 >= 256LL * 256LL));
+    p->last_kernel = use_tma ? "pruned_ring_kernel" : "pruned_fused_kernel";
     A.slots_shift = slots > 0 ? ilog2(slots) : 0;
     A.groups_shift = ilog2(g.N1 / 8);
     A.xc_shift = ilog2(A.xc);
