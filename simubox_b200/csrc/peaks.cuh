@@ -68,6 +68,12 @@ __device__ inline void peaks_block(const double* __restrict__ q, const double* _
   const int div = pp.step - 1;
   const double delta = __dsub_rn(stop, start);
   const double dx = div > 0 ? __ddiv_rn(delta, (double)div) : 0.0;
+  // width = 2^k (the default 0.5 is): 1 / width is exact, so RN(d * (1 / width)) == RN(d / width) bit for bit and
+  // the ~20-instruction division leaves the step x rows inner loop
+  const long long wbits = __double_as_longlong(pp.width);
+  const int wexp = (int)((wbits >> 52) & 0x7ff);
+  const bool w_pow2 = (wbits & 0x000fffffffffffffLL) == 0 && wexp > 0x3ff - 1000 && wexp < 0x3ff + 1000;
+  const double w_inv = w_pow2 ? __ddiv_rn(1.0, pp.width) : 0.0;
   for (int i = tid; i < pp.step; i += nthr) {
     double x;
     if (div > 0 && dx != 0.0) x = __dadd_rn(__dmul_rn((double)i, dx), start);
@@ -76,7 +82,8 @@ __device__ inline void peaks_block(const double* __restrict__ q, const double* _
     if (div > 0 && i == div) x = stop;
     double acc = 0.0;
     for (int r = 0; r < rows; ++r) {
-      const double t = __ddiv_rn(__dsub_rn(x, ctr[r]), pp.width);
+      const double d = __dsub_rn(x, ctr[r]);
+      const double t = w_pow2 ? __dmul_rn(d, w_inv) : __ddiv_rn(d, pp.width);
       const double g = __dmul_rn(amp[r], exp(-__dmul_rn(t, t)));
       acc = __dadd_rn(acc, g);
     }

@@ -270,8 +270,14 @@ __host__ __device__ inline size_t ring_fixed_bytes(int N0, int N2, size_t work_d
   return ((size_t)(N2 / 16) * 128 + 2 * (size_t)N0 + work_doubles) * sizeof(double) + kRingMaxSlots * 8;
 }
 
-__global__ void __launch_bounds__(kRingThreads, 1)
+// NW warps per CTA: 16 (one CTA per SM) or 8 (two CTAs per SM, so that one CTA's plane barriers, y / x stages and
+// field finish overlap the other's z stage).
+template <int NW>
+__global__ void __launch_bounds__(32 * NW, 16 / NW)
 pruned_ring_kernel(const FusedArgs A) {
+  constexpr int NT = 32 * NW;          // threads
+  constexpr int KQ = NW / 4;           // K splits of the y-stage product
+  constexpr int MPT = kRingThreads / NT;  // listed modes per thread (n_umodes <= kRingThreads)
   extern __shared__ __align__(128) unsigned char smraw[];
   const int S = A.ring_slots;
   const size_t slot_bytes = ring_slot_bytes(A.N2);
@@ -289,8 +295,8 @@ pruned_ring_kernel(const FusedArgs A) {
   __shared__ volatile int s_issued[kRingMaxSlots];  // how many times each slot has been requested
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   if (tid < kRingMaxSlots) s_issued[tid] = 0;
-  for (int i = tid; i < A.ds * 128; i += kRingThreads) twf[i] = A.twf[i];
-  for (int i = tid; i < A.N0; i += kRingThreads) tw0[i] = A.tw0[i];
+  for (int i = tid; i < A.ds * 128; i += NT) twf[i] = A.twf[i];
+  for (int i = tid; i < A.N0; i += NT) tw0[i] = A.tw0[i];
   if (tid < S) pf_mbar_init(&full[tid], 1);
   asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   // first plane of unit u (nullptr past the end), so that a refill needs no division
@@ -304,11 +310,17 @@ pruned_ring_kernel(const FusedArgs A) {
     s_units[1] = (int)atomicAdd(&A.ctrl[0], 1u);
     s_ubase[0] = unit_base(s_units[0]);
     s_ubase[1] = unit_base(s_units[1]);
-    s_q = 16;  // group numbers 0..15 start out with warps 0..15
+    s_q = NW;  // group numbers 0..NW-1 start out with warps 0..NW-1
   }
   // this thread's listed mode
-  const int4 md = tid < A.n_umodes ? A.umodes[tid] : make_int4(0, 0, 0, 0);
-  const int orc = md.z * 16 + (md.y < 0 ? -md.y : md.y);
+  int4 md[MPT];
+  int orc[MPT];
+#pragma unroll
+  for (int j = 0; j < MPT; ++j) {
+    const int u = tid + NT * j;
+    md[j] = u < A.n_umodes ? A.umodes[u] : make_int4(0, 0, 0, 0);
+    orc[j] = md[j].z * 16 + (md[j].y < 0 ? -md[j].y : md[j].y);
+  }
   const int m = lane >> 2, kk = lane & 3;
   const int groups = A.N1 >> 3;
   const int n_units = A.n_fields * A.chunks;
@@ -335,7 +347,7 @@ pruned_ring_kernel(const FusedArgs A) {
       }
     }
   };
-  for (int q = warp; q < S; q += 16) issue(q);
+  for (int q = warp; q < S; q += NW) issue(q);
   int myq = warp;
 
   for (int k = 0;; ++k) {
@@ -348,8 +360,13 @@ pruned_ring_kernel(const FusedArgs A) {
     }
     const int field = unit / A.chunks, chunk = unit - field * A.chunks;
     const int x0 = chunk * A.xc;
-    double fr = 0.0, fi = 0.0;
-    int jj = (int)(((long long)md.x * x0) % A.N0);
+    double fr[MPT], fi[MPT];
+    int jj[MPT];
+#pragma unroll
+    for (int j = 0; j < MPT; ++j) {
+      fr[j] = 0.0; fi[j] = 0.0;
+      jj[j] = (int)(((long long)md[j].x * x0) % A.N0);
+    }
     for (int xi = 0; xi < A.xc; ++xi) {
       const int plane_start = (k * A.xc + xi) * groups, plane_end = plane_start + groups;
       // ---- stage 1 (z, folded): warps take group numbers until the plane is used up
@@ -386,10 +403,10 @@ pruned_ring_kernel(const FusedArgs A) {
         myq = __shfl_sync(0xffffffffu, nq, 0);
       }
       __syncthreads();
-      // ---- stage 2 (y): 16 x 16 x N1 product, 4 output tiles x 4 K quarters over the 16 warps
+      // ---- stage 2 (y): 16 x 16 x N1 product, 4 output tiles x KQ K-parts over the warps
       {
         const int mt = warp & 1, nt = (warp >> 1) & 1, kh = warp >> 2;
-        const int s0 = kh * (A.ks1 >> 2), s1 = s0 + (A.ks1 >> 2);
+        const int s0 = kh * (A.ks1 / KQ), s1 = s0 + (A.ks1 / KQ);
         const double* arow = gT + (size_t)(8 * mt + m) * A.gstride;
         const double* brow = A.tw1 + (size_t)nt * A.ks1 * 32;
         double d0 = 0.0, d1 = 0.0;
@@ -399,24 +416,34 @@ pruned_ring_kernel(const FusedArgs A) {
         if (kh > 0) { c2[(kh - 1) * 256 + r * 16 + c] = d0; c2[(kh - 1) * 256 + r * 16 + c + 1] = d1; }
         __syncthreads();
         if (kh == 0) {
-          hp[r * 16 + c] = ((d0 + c2[r * 16 + c]) + c2[256 + r * 16 + c]) + c2[512 + r * 16 + c];
-          hp[r * 16 + c + 1] = ((d1 + c2[r * 16 + c + 1]) + c2[256 + r * 16 + c + 1]) + c2[512 + r * 16 + c + 1];
+#pragma unroll
+          for (int j = 0; j < KQ - 1; ++j) {
+            d0 += c2[j * 256 + r * 16 + c];
+            d1 += c2[j * 256 + r * 16 + c + 1];
+          }
+          hp[r * 16 + c] = d0;
+          hp[r * 16 + c + 1] = d1;
         }
       }
       __syncthreads();
       // ---- stage 3 (x): one thread per listed mode
-      if (tid < A.n_umodes) {
-        const double rc = hp[orc], rs = hp[orc + 8], sc = hp[orc + 128], ss = hp[orc + 136];
-        const double hr = md.y >= 0 ? rc - ss : rc + ss;
-        const double hi = md.y >= 0 ? -(rs + sc) : rs - sc;
-        const double2 w = tw0[jj];
-        fr += hr * w.x + hi * w.y;
-        fi += hi * w.x - hr * w.y;
-        jj += md.x;
-        if (jj >= A.N0) jj -= A.N0;
+#pragma unroll
+      for (int j = 0; j < MPT; ++j) {
+        if (tid + NT * j < A.n_umodes) {
+          const double rc = hp[orc[j]], rs = hp[orc[j] + 8], sc = hp[orc[j] + 128], ss = hp[orc[j] + 136];
+          const double hr = md[j].y >= 0 ? rc - ss : rc + ss;
+          const double hi = md[j].y >= 0 ? -(rs + sc) : rs - sc;
+          const double2 w = tw0[jj[j]];
+          fr[j] += hr * w.x + hi * w.y;
+          fi[j] += hi * w.x - hr * w.y;
+          jj[j] += md[j].x;
+          if (jj[j] >= A.N0) jj[j] -= A.N0;
+        }
       }
     }
-    if (tid < A.n_umodes) A.partial[(long long)unit * A.n_umodes + tid] = make_double2(fr, fi);
+#pragma unroll
+    for (int j = 0; j < MPT; ++j)
+      if (tid + NT * j < A.n_umodes) A.partial[(long long)unit * A.n_umodes + tid + NT * j] = make_double2(fr[j], fi[j]);
     __threadfence();
     __syncthreads();
     if (tid == 0) s_last = atomicAdd(&A.ctrl[1 + field], 1u) == (unsigned)(A.chunks - 1);

@@ -466,7 +466,8 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   cudaFuncSetAttribute(pruned_planes_fullk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
-  cudaFuncSetAttribute(pruned_ring_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
+  cudaFuncSetAttribute(pruned_ring_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
+  cudaFuncSetAttribute(pruned_ring_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
@@ -560,12 +561,21 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
     static const int tma_on = [] { const char* e = getenv("SBX_FUSED_TMA"); return e ? atoi(e) : 1; }();
     const size_t rwork = ring_work_doubles(g.N1, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks);
     const size_t rfixed = ring_fixed_bytes(g.N0, g.N2, rwork);
-    int slots = rfixed < kMaxTmaSmem ? (int)((kMaxTmaSmem - rfixed) / ring_slot_bytes(g.N2)) : 0;
-    slots = std::min(slots, std::min(kRingMaxSlots, A.xc * (g.N1 / 8)));  // refills look at most one unit ahead
-    if (const char* e = getenv("SBX_RING_SLOTS")) slots = std::min(slots, std::max(1, atoi(e)));
     auto ilog2 = [](int v) { int l = 0; while ((1 << (l + 1)) <= v) ++l; return l; };
     auto pow2 = [](int v) { return v > 0 && (v & (v - 1)) == 0; };
-    slots = slots > 0 ? 1 << ilog2(slots) : 0;  // power of two: slot = q & (S - 1)
+    // ring size for a CTA that may use `budget` bytes: a power of two (slot = q & (S - 1)), at most one unit ahead
+    auto ring_slots_for = [&](size_t budget) {
+      int sl = rfixed < budget ? (int)((budget - rfixed) / ring_slot_bytes(g.N2)) : 0;
+      sl = std::min(sl, std::min(kRingMaxSlots, A.xc * (g.N1 / 8)));
+      if (const char* e = getenv("SBX_RING_SLOTS")) sl = std::min(sl, std::max(1, atoi(e)));
+      return sl > 0 ? 1 << ilog2(sl) : 0;
+    };
+    // two 8-warp CTAs per SM when each still gets a ring of >= 8 slots (one CTA's barriers, y / x stages and field
+    // finish then overlap the other's z stage), else one 16-warp CTA per SM
+    static const int ring_warps = [] { const char* e = getenv("SBX_RING_WARPS"); return e ? atoi(e) : 0; }();
+    const int slots8 = ring_slots_for(kMaxTmaSmem / 2 - 1024), slots16 = ring_slots_for(kMaxTmaSmem);
+    const int nw = ring_warps == 8 || ring_warps == 16 ? ring_warps : (slots8 >= 8 ? 8 : 16);
+    int slots = nw == 8 ? slots8 : slots16;
     // Measured on B200 (profiles/r01): the ring wins from 256^2 planes on (0.81 vs 0.98 ms per 32 x 256^3), the
     // 3-CTA/SM LDG kernel on smaller planes (0.94 vs 1.06 ms per 256 x 128^3); SBX_FUSED_TMA=2 forces the ring.
     const bool ring_fits = g.N1 % 16 == 0 && pow2(g.N1 / 8) && pow2(A.xc) && p->n_umodes <= kRingThreads && slots >= 4;
@@ -590,8 +600,9 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
       const int grid1 = (int)std::min<long long>(units, (long long)p->pruned_ctas_per_sm * p->sm_count);
       if (p->profiling) prof_event(p, st);
       if (use_tma) {
-        const int grid2 = (int)std::min<long long>(units, (long long)p->sm_count);
-        pruned_ring_kernel<<<grid2, kRingThreads, smem_tma, st>>>(A);
+        const int grid2 = (int)std::min<long long>(units, (long long)p->sm_count * (16 / nw));
+        if (nw == 8) pruned_ring_kernel<8><<<grid2, 256, smem_tma, st>>>(A);
+        else pruned_ring_kernel<16><<<grid2, 512, smem_tma, st>>>(A);
       } else
       pruned_fused_kernel<<<grid1, 256, smem, st>>>(A);
       SBX_CUDA(cudaGetLastError());

@@ -190,6 +190,23 @@ def test_pruned_dft_vs_oracle(sbx_lib, torch_cuda, shape, L, cutoff, path):
         check_scatter_rows(qI, ref, cutoff, last_shell_members(mat, L, cutoff, 1e-12))
 
 
+@pytest.mark.parametrize("width", [0.5, 0.25, 0.3, 1.7, 2.0])
+def test_peak_width_forms_vs_oracle(sbx_lib, torch_cuda, width):
+    """Gaussian broadening with power-of-two widths (exact reciprocal multiply on the device) and general widths
+    (true division): plot_y within 1e-12 relative of the numpy oracle, peak indices exact; all four paths."""
+    from simubox_b200 import synth
+
+    shape, L = (32, 32, 32), synth.box_for(2)
+    mat = synth.field_numpy(7, shape, cells=2)
+    ref, _ = scatter_np.scattering_peak_table(mat, L, 30, 1e-12)
+    kw = dict(width=width, step=700, cutoff=20, min_height=1e-6)
+    want = scatter_np.show_peak(ref, **kw)
+    for path in (DENSE, GATHER, PRUNED, FUSED):
+        out = run_scatter(sbx_lib, torch_cuda, [mat], L, 30, 1e-12, path, peaks=kw)
+        n = int(out["n_peaks"][0])
+        assert np.array_equal(out["peak_idx"][0, :n].cpu().numpy(), want["peaks_index"]), path
+
+
 def test_auto_path_selection(sbx_lib, torch_cuda):
     from simubox_b200.scatter import get_plan
 
