@@ -94,6 +94,36 @@ def fields_torch(first: int, count: int, shape=(128, 128, 128), cells: int = 2, 
     return out
 
 
+def field_planes_torch(index: int, shape, x0: int, x1: int, cells: int = 2, device="cuda", noise: float = 1e-3):
+    """Planes x0..x1-1 of field ``index`` as a (x1-x0, N1, N2) fp64 tensor: the same values ``fields_torch``
+    produces, generated slab by slab (a 1024^3 field never exists in one piece on one rank)."""
+    import torch
+
+    dev = torch.device(device)
+    N0, N1, N2 = (int(n) for n in shape)
+    ax = [2 * torch.pi * cells * torch.arange(n, device=dev, dtype=torch.float64) / n for n in (N0, N1, N2)]
+    X, Y, Z = torch.meshgrid(ax[0][x0:x1], ax[1], ax[2], indexing="ij")
+    if index % 2 == 0:
+        s = torch.sin(X) * torch.cos(Y) + torch.sin(Y) * torch.cos(Z) + torch.sin(Z) * torch.cos(X)
+    else:
+        s = torch.cos(X) * torch.cos(Y) + torch.cos(Y) * torch.cos(Z) + torch.cos(Z) * torch.cos(X)
+    t, w = field_params(index)
+    vox = torch.arange(x0 * N1 * N2, x1 * N1 * N2, device=dev, dtype=torch.int64)
+
+    def wrap(c):
+        return c - (1 << 64) if c >= (1 << 63) else c
+
+    def lsr(z, k):
+        return (z >> k) & ((1 << (64 - k)) - 1)
+
+    z = vox + wrap((index * 0x632BE59BD9B4E019) & _MASK64) + wrap(0x9E3779B97F4A7C15)
+    z = (z ^ lsr(z, 30)) * wrap(0xBF58476D1CE4E5B9)
+    z = (z ^ lsr(z, 27)) * wrap(0x94D049BB133111EB)
+    z = z ^ lsr(z, 31)
+    u = lsr(z, 11).to(torch.float64) * (1.0 / (1 << 53)) - 0.5
+    return torch.sigmoid((s - t) / w) + noise * u.reshape(x1 - x0, N1, N2)
+
+
 def seeds_lattice(shape=(256, 256, 256), per_axis: int = 16, jitter: float = 4.0, seed: int = 1234):
     """Jittered lattice of domain centres: centres at
     spacing*(a+1/2) voxel units plus uniform jitter in [-jitter, jitter), a-major order."""

@@ -32,7 +32,8 @@ def main():
     local_slab = torch.from_numpy(np.ascontiguousarray(mat[lo:hi])).cuda(local)
     qI = slab.q_intensity(local_slab)
     qI2 = slab.q_intensity(local_slab)  # plan re-use
-    assert np.array_equal(qI, qI2)
+    # the dense histogram accumulates with atomics: order, hence the last bits, may differ between runs
+    assert np.array_equal(qI[:, 0], qI2[:, 0]) and np.allclose(qI[:, 1], qI2[:, 1], rtol=1e-12, atol=1e-12 * np.abs(qI[:, 1]).max())
     rows = [None] * world
     dist.all_gather_object(rows, qI[:, 1].tolist())
     assert all(r == rows[0] for r in rows), "ranks disagree on the all-reduced shell sums"
