@@ -184,6 +184,20 @@ int sbx_scatter_slab_plan_destroy(sbx_slab_plan* plan);
 int sbx_scatter_slab_emulate(int device, int world, const int64_t* N, const double* L, int cutoff,
                              double threshold, const double* field, double* shell_I, void* stream);
 
+/* ---- phin / phout text reader (host code, no device needed) ---------------------------------
+ * Replaces pd.read_csv(path, skiprows=skip, header=None, sep="[ ]+", engine="python")
+ * (SimuBox/toolkit/reader.py:170-172).  buf = the whole file in host memory.  `skip` header lines are
+ * skipped, blank lines ignored, tokens are blank-separated and converted with correctly rounded
+ * decimal->double conversion (the doubles Python's float() gives).  threads <= 0: one per core.
+ * shape: rows = non-blank lines after the header, cols = tokens of the first of them.
+ * parse: out = rows x cols fp64, C order; SBX_EINVAL when a row has another width or a token is not a
+ * number (the Python layer raises ValueError, which drives the reference's header-guess retry,
+ * reader.py:173-186).  is_ascii: 1 when every byte < 0x80 (then the file certainly decodes as UTF-8). */
+int sbx_text_is_ascii(const char* buf, int64_t len);
+int sbx_text_table_shape(const char* buf, int64_t len, int skip, int threads, int64_t* rows, int32_t* cols);
+int sbx_text_table_parse(const char* buf, int64_t len, int skip, int64_t rows, int32_t cols, double* out,
+                         int threads);
+
 #ifdef __cplusplus
 }
 #endif

@@ -54,10 +54,47 @@ def _bad_grid(vec: np.ndarray) -> bool:
     return bool(np.any(vec > 1000) or np.any(vec <= 0))
 
 
-def _load_text_table(path: Path, skip: int) -> np.ndarray:
-    """Blank-separated numeric rows -> (rows, ncol) fp64.  numpy's C tokenizer parses with
-    correctly rounded strtod, i.e. the same doubles Python's float() gives the reference."""
-    return np.loadtxt(path, dtype=np.float64, skiprows=skip, ndmin=2, comments=None)
+def _file_bytes(path: Path) -> np.ndarray:
+    return np.fromfile(path, dtype=np.uint8)
+
+
+def _load_text_table(raw: np.ndarray, skip: int, threads: int = 0) -> np.ndarray:
+    """Blank-separated numeric rows -> (rows, ncol) fp64 through the native multithreaded parser
+    (csrc/text_table.cpp: correctly rounded conversion = the doubles Python's float() gives the
+    reference's pandas python-engine parse, reader.py:170-172).  ValueError on ragged or
+    non-numeric rows, like the reference's parse."""
+    import ctypes as C
+
+    from . import _lib
+
+    L_ = _lib.lib()
+    ptr, n = C.c_void_p(raw.ctypes.data), C.c_int64(raw.size)
+    rows, cols = C.c_int64(), C.c_int32()
+    _lib.check(L_.sbx_text_table_shape(ptr, n, skip, threads, C.byref(rows), C.byref(cols)))
+    if rows.value == 0 or cols.value == 0:
+        return np.empty((0, 0), dtype=np.float64)
+    out = np.empty((rows.value, cols.value), dtype=np.float64)
+    rc = L_.sbx_text_table_parse(ptr, n, skip, rows, cols, out.ctypes.data_as(C.POINTER(C.c_double)), threads)
+    if rc != 0:
+        raise ValueError((L_.sbx_last_error() or b"").decode())
+    return out
+
+
+def _decodes(raw: np.ndarray, encoding: str) -> bool:
+    """The reference decodes the whole file and treats a UnicodeDecodeError as "binary" (reader.py:107,
+    115-125).  Pure-ASCII bytes decode under every ASCII-compatible codec: checked natively; otherwise decode."""
+    import ctypes as C
+
+    from . import _lib
+
+    if _lib.lib().sbx_text_is_ascii(C.c_void_p(raw.ctypes.data), C.c_int64(raw.size)) == 1 and \
+            encoding.lower().replace("_", "-") in ("utf-8", "utf8", "ascii", "latin-1", "latin1", "gbk", "gb2312", "gb18030", "cp936"):
+        return True
+    try:
+        raw.tobytes().decode(encoding)
+        return True
+    except UnicodeDecodeError:
+        return False
 
 
 def read_density(path: FileLike, parse_N: bool = True, parse_L: bool = False,
@@ -74,14 +111,16 @@ def read_density(path: FileLike, parse_N: bool = True, parse_L: bool = False,
             text = False
         else:
             text = True
-            try:
-                with path.open(mode=mode, encoding=encoding) as fh:
-                    header = [fh.readline() for _ in range(2)]
-                    for _ in fh:  # the reference decodes the whole file; undecodable => binary
-                        pass
-            except UnicodeDecodeError:
+            text_raw = _file_bytes(path)
+            if not _decodes(text_raw, encoding):
                 return read_density(path, parse_N=True, parse_L=True, filename=filename, mode=mode,
                                     encoding=encoding, binary=True, **kwargs)
+            pos = 0
+            for _ in range(2):  # the two possible header lines
+                nl = np.flatnonzero(text_raw[pos:pos + 4096] == 10)
+                end = pos + int(nl[0]) + 1 if len(nl) else len(text_raw)
+                header.append(text_raw[pos:end].tobytes().decode(encoding))
+                pos = end
     else:
         raise ValueError(type(path))
 
@@ -123,7 +162,7 @@ def read_density(path: FileLike, parse_N: bool = True, parse_L: bool = False,
     retry = dict(parse_N=True, parse_L=True, filename=filename, mode=mode, encoding=encoding, binary=binary)
     if text:
         try:
-            table = _load_text_table(path, skip)
+            table = _load_text_table(text_raw, skip, int(kwargs.get("threads", 0)))
         except ValueError:
             # ragged first rows: the caller guessed the header length wrong (reader.py:173-186)
             if not parse_L or not parse_N:
