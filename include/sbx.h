@@ -184,6 +184,19 @@ int sbx_scatter_slab_plan_destroy(sbx_slab_plan* plan);
 int sbx_scatter_slab_emulate(int device, int world, const int64_t* N, const double* L, int cutoff,
                              double threshold, const double* field, double* shell_I, void* stream);
 
+/* ---- per-cell statistics on a label grid (device pointers) -------------------------------------
+ * What the reference derives downstream of its Voronoi / Delaunay constructions
+ * (SimuBox/calculator/voronoi.py:150-213 coord_dict; demos/scripts.ipynb cells 1-2 in-cell densities),
+ * computed from the int32 label array sbx_voronoi_label writes (label < 0 = masked voxel, skipped):
+ *   volume[s]  voxels labelled s;  mass[s]  sum of field over them (field/mass may be NULL);
+ *   adjacency  n_cells x ceil(n_cells/32) uint32 bit matrix, bit (s,t) set iff two face-adjacent
+ *              voxels (wrap-around when periodic != 0) carry labels s and t (NULL = skip);
+ *   degree[s]  number of set bits of row s (needs adjacency).
+ * All outputs are overwritten.  Asynchronous on `stream`. */
+int sbx_cell_stats(int device, int ndim, const int64_t* N, const int32_t* labels, const double* field,
+                   int64_t n_cells, int periodic, int64_t* volume, double* mass, uint32_t* adjacency,
+                   int32_t* degree, void* stream);
+
 /* ---- phin / phout text reader (host code, no device needed) ---------------------------------
  * Replaces pd.read_csv(path, skiprows=skip, header=None, sep="[ ]+", engine="python")
  * (SimuBox/toolkit/reader.py:170-172).  buf = the whole file in host memory.  `skip` header lines are

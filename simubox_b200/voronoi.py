@@ -125,6 +125,55 @@ class VoronoiCell:
         return out
 
     @classmethod
+    def cell_statistics(cls, labels, field=None, n_cells: Optional[int] = None, periodic: bool = True,
+                        neighbours: bool = True, device: int = 0) -> dict:
+        """Per-cell statistics of a label grid (``label_grid`` output; label < 0 = masked voxel).
+
+        Returns ``volume`` (int64 voxels per cell), ``mass`` (sum of ``field`` per cell, when a field is
+        given) and, with ``neighbours``, the face-adjacency graph of the cells: ``degree`` (coordination
+        number per cell), ``indptr`` / ``indices`` (CSR neighbour lists, ascending) and ``coord_dict``
+        (cell -> set of neighbours, the structure ``VoronoiCell.triangle`` returns from Delaunay
+        triangles, reference voronoi.py:178-182).  ``periodic``: neighbours wrap around the grid.
+        """
+        torch = torch_cuda()
+        lab = to_device(labels if isinstance(labels, torch.Tensor) else np.ascontiguousarray(labels, dtype=np.int32), device, torch.int32)
+        lab = lab.contiguous()
+        shape = tuple(int(n) for n in lab.shape)
+        if len(shape) not in (2, 3):
+            raise ValueError(f"labels must be a 2D or 3D grid, got shape {shape}")
+        f = None
+        if field is not None:
+            f = to_device(field if isinstance(field, torch.Tensor) else np.ascontiguousarray(field, dtype=np.float64), device, torch.float64)
+            f = f.contiguous()
+            if tuple(f.shape) != shape:
+                raise ValueError(f"field shape {tuple(f.shape)} != labels {shape}")
+        if n_cells is None:
+            n_cells = int(lab.max().item()) + 1
+        n_cells = int(n_cells)
+        if n_cells < 1:
+            raise ValueError("no labelled voxel")
+        words = (n_cells + 31) // 32
+        vol = torch.empty(n_cells, dtype=torch.int64, device=lab.device)
+        mass = torch.empty(n_cells, dtype=torch.float64, device=lab.device) if f is not None else None
+        adj = torch.empty((n_cells, words), dtype=torch.int32, device=lab.device) if neighbours else None
+        deg = torch.empty(n_cells, dtype=torch.int32, device=lab.device) if neighbours else None
+        _, pn = _lib.i64(shape)
+        _lib.check(_lib.lib().sbx_cell_stats(device, len(shape), pn, ptr(lab), ptr(f), n_cells, int(bool(periodic)),
+                                             ptr(vol), ptr(mass), ptr(adj), ptr(deg), stream_ptr(device)))
+        out = dict(volume=vol.cpu().numpy(), n_cells=n_cells)
+        if mass is not None:
+            out["mass"] = mass.cpu().numpy()
+        if neighbours:
+            bits = np.unpackbits(adj.cpu().numpy().view(np.uint8), axis=1, bitorder="little")[:, :n_cells]
+            rows, cols = np.nonzero(bits)
+            degree = deg.cpu().numpy()
+            indptr = np.zeros(n_cells + 1, dtype=np.int64)
+            np.cumsum(degree, out=indptr[1:])
+            out.update(degree=degree, indptr=indptr, indices=cols.astype(np.int32),
+                       coord_dict={int(s): set(cols[indptr[s]:indptr[s + 1]].tolist()) for s in range(n_cells) if degree[s]})
+        return out
+
+    @classmethod
     def weighted_voronoi_diagrams(cls, points, weights=0, method: WeightedMode = WeightedMode.ADDITIVE,
                                   size: Tuple = (500, 500), color_mode: ColorMode = ColorMode.L,
                                   interactive: bool = True, num_threads: int = 8, **kwargs):
