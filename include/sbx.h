@@ -197,6 +197,20 @@ int sbx_cell_stats(int device, int ndim, const int64_t* N, const int32_t* labels
                    int64_t n_cells, int periodic, int64_t* volume, double* mass, uint32_t* adjacency,
                    int32_t* degree, void* stream);
 
+/* ---- periodic domain-centre finder (device pointers; n_components_host is a host pointer) -------
+ * 3D-capable replacement for the seed finding of VoronoiCell.OpenCV (SimuBox/calculator/voronoi.py:31-68:
+ * 3 x 3 tiling + cv2 threshold + contour moments, 2D only): foreground = field > threshold, connected
+ * components under face connectivity with wrap-around when periodic != 0, centroid of every component
+ * = root + mean minimum-image displacement (integer sums: bit-reproducible), wrapped into [0, N).
+ * Components are ordered by their smallest voxel index.
+ *   comp_labels  Nxyz int32 out, component id per voxel, -1 background (NULL = not wanted)
+ *   centres      max_components x ndim fp64 (voxel units), volumes max_components int64 (NULL ok)
+ *   *n_components_host = number of components found; only the first max_components are written.
+ * Synchronises on `stream` (it has to return the count). */
+int sbx_domain_centres(int device, int ndim, const int64_t* N, const double* field, double threshold,
+                       int periodic, int32_t* comp_labels, int64_t max_components, double* centres,
+                       int64_t* volumes, int64_t* n_components_host, void* stream);
+
 /* ---- phin / phout text reader (host code, no device needed) ---------------------------------
  * Replaces pd.read_csv(path, skiprows=skip, header=None, sep="[ ]+", engine="python")
  * (SimuBox/toolkit/reader.py:170-172).  buf = the whole file in host memory.  `skip` header lines are

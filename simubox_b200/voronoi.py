@@ -125,6 +125,47 @@ class VoronoiCell:
         return out
 
     @classmethod
+    def domain_centres(cls, field, threshold: Optional[float] = None, periodic: bool = True, min_voxels: int = 1,
+                       device: int = 0, return_labels: bool = False) -> dict:
+        """Domain centres of a 2D or 3D field: connected components of ``field > threshold`` (faces,
+        wrap-around when ``periodic``) and their centroids in voxel units -- the 3D-capable counterpart
+        of ``VoronoiCell.OpenCV`` (reference voronoi.py:31-68, 2D only, 3 x 3 tiling + cv2 moments).
+
+        ``threshold`` defaults to the mid-range ``(min + max) / 2`` of the field.  Components with fewer
+        than ``min_voxels`` voxels are dropped from ``centres`` / ``volumes`` (their ids stay in
+        ``labels``).  Returns dict(centres (S, d), volumes (S,), ids (S,), n_components[, labels]).
+        Feed ``centres`` to ``label_grid(points=centres, box=shape)``.
+        """
+        torch = torch_cuda()
+        f = to_device(field if isinstance(field, torch.Tensor) else np.ascontiguousarray(field, dtype=np.float64), device, torch.float64)
+        f = f.contiguous()
+        shape = tuple(int(n) for n in f.shape)
+        nd = len(shape)
+        if nd not in (2, 3):
+            raise ValueError(f"field must be 2D or 3D, got shape {shape}")
+        if threshold is None:
+            threshold = 0.5 * (float(f.min().item()) + float(f.max().item()))
+        comp = torch.empty(shape, dtype=torch.int32, device=f.device) if return_labels else None
+        _, pn = _lib.i64(shape)
+        cap = 4096
+        while True:
+            centres = torch.empty((cap, nd), dtype=torch.float64, device=f.device)
+            volumes = torch.empty(cap, dtype=torch.int64, device=f.device)
+            n = C.c_int64()
+            _lib.check(_lib.lib().sbx_domain_centres(device, nd, pn, ptr(f), float(threshold), int(bool(periodic)), ptr(comp),
+                                                     cap, ptr(centres), ptr(volumes), C.byref(n), stream_ptr(device)))
+            if n.value <= cap:
+                break
+            cap = int(n.value)
+        S = int(n.value)
+        c, v = centres[:S].cpu().numpy(), volumes[:S].cpu().numpy()
+        keep = v >= int(min_voxels)
+        out = dict(centres=c[keep], volumes=v[keep], ids=np.flatnonzero(keep).astype(np.int32), n_components=S, threshold=float(threshold))
+        if return_labels:
+            out["labels"] = comp.cpu().numpy()
+        return out
+
+    @classmethod
     def cell_statistics(cls, labels, field=None, n_cells: Optional[int] = None, periodic: bool = True,
                         neighbours: bool = True, device: int = 0) -> dict:
         """Per-cell statistics of a label grid (``label_grid`` output; label < 0 = masked voxel).

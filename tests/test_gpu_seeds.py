@@ -1,0 +1,112 @@
+"""GPU parity suite for the periodic domain-centre finder (csrc/seeds.cu) against oracle/seeds_np.py:
+component labels, ordering, volumes and centroids bit-exact (integer sums); end to end into the labelling kernel."""
+import numpy as np
+import pytest
+
+from oracle import seeds_np
+
+pytestmark = pytest.mark.gpu
+
+
+def blobs(shape, centres, radius, periodic=True):
+    grids = np.meshgrid(*[np.arange(n) for n in shape], indexing="ij")
+    f = np.zeros(shape)
+    for c in centres:
+        d2 = 0
+        for g, cc, n in zip(grids, c, shape):
+            d = np.abs(g - cc)
+            if periodic:
+                d = np.minimum(d, n - d)
+            d2 = d2 + d ** 2
+        f = np.maximum(f, np.exp(-d2 / (2 * radius ** 2)))
+    return f
+
+
+@pytest.mark.parametrize("shape,periodic", [((24, 24, 24), True), ((24, 24, 24), False), ((20, 36), True), ((33, 17), False),
+                                            ((6, 40, 9), True), ((1, 16, 16), True), ((2, 2, 2), True)])
+def test_random_foreground_vs_oracle(sbx_lib, shape, periodic):
+    """Random foreground at the percolation-ish density: many ragged components, several wrapping around."""
+    from simubox_b200 import VoronoiCell
+
+    rng = np.random.default_rng(sum(shape) + periodic)
+    field = rng.random(shape)
+    thr = 0.62
+    got = VoronoiCell.domain_centres(field, thr, periodic=periodic, return_labels=True)
+    want = seeds_np.domain_centres(field, thr, periodic=periodic)
+    assert got["n_components"] == want["n_components"]
+    assert np.array_equal(got["labels"], want["labels"])
+    assert np.array_equal(got["volumes"], want["volumes"])
+    assert np.array_equal(got["centres"], want["centres"])  # integer sums + one division: bit for bit
+
+
+def test_blobs_across_the_boundary_and_min_voxels(sbx_lib):
+    from simubox_b200 import VoronoiCell
+
+    shape = (32, 32, 32)
+    true = np.array([[0.0, 0.0, 0.0], [16.0, 31.5, 8.0], [8.0, 16.0, 31.0], [24.0, 8.0, 16.5]])
+    field = blobs(shape, true, 2.0)
+    field[5, 5, 20] = 1.0  # a single-voxel speck
+    got = VoronoiCell.domain_centres(field, 0.5, min_voxels=2)
+    assert got["n_components"] == 5 and len(got["centres"]) == 4
+    for c in got["centres"]:
+        d = np.abs(true - c)
+        d = np.minimum(d, 32 - d)
+        assert np.sqrt((d ** 2).sum(axis=1)).min() < 0.3
+    want = seeds_np.domain_centres(field, 0.5)
+    assert np.array_equal(got["centres"], want["centres"][want["volumes"] >= 2])
+    # non-periodic: the blob at the origin falls apart into 8 corner pieces
+    assert VoronoiCell.domain_centres(field, 0.5, periodic=False)["n_components"] > 5
+
+
+def test_more_components_than_the_first_buffer(sbx_lib):
+    from simubox_b200 import VoronoiCell
+
+    field = np.zeros((64, 64, 8))
+    field[::2, ::2, ::2] = 1.0  # 4096 isolated voxels ... plus one more
+    field[1, 1, 1] = 1.0
+    got = VoronoiCell.domain_centres(field, 0.5)
+    want = seeds_np.domain_centres(field, 0.5)
+    assert got["n_components"] == 4097 == want["n_components"]
+    assert np.array_equal(got["centres"], want["centres"])
+
+
+def test_seeds_feed_the_labelling_kernel_at_baseline_size(sbx_lib):
+    """256^3 BCC-like field -> centres -> periodic Voronoi labels: every domain voxel carries the label of its own
+    component's centre (domains are compact and well separated), 2 * 4^3 = 128 spheres."""
+    import torch
+
+    from simubox_b200 import VoronoiCell, synth
+
+    shape = (256, 256, 256)
+    field = synth.fields_torch(1, 1, shape, cells=4)[0]  # odd index: BCC level set, minority spheres
+    res = VoronoiCell.domain_centres(field, 0.5, return_labels=True)
+    S = res["n_components"]
+    assert S == 128, S
+    assert int(res["volumes"].sum()) == int((field > 0.5).sum().item())
+    lab = VoronoiCell.label_grid(res["centres"], 0, shape=shape, box=(256.0,) * 3)
+    comp = res["labels"]
+    inside = comp >= 0
+    assert np.array_equal(lab[inside], comp[inside])
+    st = VoronoiCell.cell_statistics(lab, field, n_cells=S)
+    assert st["volume"].sum() == 256 ** 3 and st["degree"].min() >= 8  # BCC: 8 hexagonal + 6 square faces
+
+
+def test_agrees_with_opencv_moments_on_separated_2d_blobs(sbx_lib):
+    cv2 = pytest.importorskip("cv2")
+    from simubox_b200 import VoronoiCell
+
+    shape = (96, 96)
+    rng = np.random.default_rng(3)
+    true = np.array([[a * 24 + 12 + rng.uniform(-3, 3), b * 24 + 12 + rng.uniform(-3, 3)] for a in range(4) for b in range(4)])
+    field = blobs(shape, true, 4.0)
+    got = VoronoiCell.domain_centres(field, 0.5)
+    img = (field > 0.5).astype(np.uint8) * 255
+    contours, _ = cv2.findContours(img, cv2.RETR_EXTERNAL, cv2.CHAIN_APPROX_NONE)
+    cvc = []
+    for c in contours:
+        m = cv2.moments(c)
+        cvc.append([m["m01"] / m["m00"], m["m10"] / m["m00"]])  # (row, col)
+    cvc = np.array(cvc)
+    assert len(cvc) == len(got["centres"]) == 16
+    for c in got["centres"]:
+        assert np.sqrt(((cvc - c) ** 2).sum(axis=1)).min() < 0.5
