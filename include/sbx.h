@@ -211,6 +211,14 @@ int sbx_domain_centres(int device, int ndim, const int64_t* N, const double* fie
                        int periodic, int32_t* comp_labels, int64_t max_components, double* centres,
                        int64_t* volumes, int64_t* n_components_host, void* stream);
 
+/* ---- particle -> grid density splat (device pointers; N, L host) --------------------------------
+ * XmlTransformer.transform (SimuBox/toolkit/xmltrans.py:117-153): every particle adds 1 to each grid point of
+ * its type's density within r_cut, with the reference's stencil, base-index and wrapped-coordinate
+ * arithmetic (bit-identical counts).  xyz: P x 3 fp64 in [-L/2, L/2); type: P int32 in [0, n_types)
+ * (others are skipped); phi: n_types x N0 x N1 x N2 fp64, overwritten.  Asynchronous on `stream`. */
+int sbx_particle_splat(int device, const double* xyz, const int32_t* type, int64_t n_particles, int n_types,
+                       const int64_t* N, const double* L, double r_cut, double* phi, void* stream);
+
 /* ---- phin / phout text reader (host code, no device needed) ---------------------------------
  * Replaces pd.read_csv(path, skiprows=skip, header=None, sep="[ ]+", engine="python")
  * (SimuBox/toolkit/reader.py:170-172).  buf = the whole file in host memory.  `skip` header lines are

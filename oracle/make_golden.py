@@ -203,6 +203,46 @@ def gen_reader():
                         inCompMax=po.inCompMax)
 
 
+def write_snapshot(path, xyz, types, L):
+    """Minimal HOOMD/GALAMOST-style xml the reference's XmlTransformer reads (xmltrans.py:25-61)."""
+    body = ["<?xml version=\"1.0\" encoding=\"UTF-8\"?>", "<galamost_xml version=\"1.3\">",
+            f"<configuration time_step=\"0\" dimensions=\"3\" natoms=\"{len(xyz)}\" >",
+            f"<box lx=\"{float(L[0])!r}\" ly=\"{float(L[1])!r}\" lz=\"{float(L[2])!r}\"/>", f"<position num=\"{len(xyz)}\">"]
+    body += [" ".join(repr(float(v)) for v in p) for p in xyz]
+    body += ["</position>", f"<type num=\"{len(xyz)}\">"] + list(types) + ["</type>", "</configuration>", "</galamost_xml>"]
+    Path(path).write_text("\n".join(body) + "\n")
+
+
+def gen_splat():
+    """XmlTransformer.parse_xml + transform of the live reference on small synthetic snapshots."""
+    from oracle import splat_np
+
+    sb = ref_live.load()
+    files = OUT / "files"
+    rng = np.random.default_rng(2024)
+    cases = {"splat_cubic": dict(L=(8.0, 8.0, 8.0), P=300, N=None, r_cut=2.0),
+             "splat_noncubic_fine": dict(L=(6.5, 9.0, 5.2), P=200, N=(12, 10, 14), r_cut=1.3),
+             "splat_coarse": dict(L=(10.0, 10.0, 12.0), P=150, N=(6, 4, 8), r_cut=2.5)}
+    for name, c in cases.items():
+        L = np.array(c["L"])
+        xyz = (rng.random((c["P"], 3)) - 0.5) * L
+        xyz[:6] = [[-L[0] / 2, 0, 0], [L[0] / 2 - 1e-9, 0.1, 0.2], [0, -L[1] / 2, L[2] / 2 - 1e-12], [0.0, 0.0, 0.0],
+                   [-L[0] / 2 + 0.5, -L[1] / 2 + 0.5, -L[2] / 2 + 0.5], [L[0] / 4, L[1] / 4, L[2] / 4]]
+        # digits in type names only work with merge=False (with merge=True the reference maps the stripped names and
+        # leaves "A1" unmapped -> NaN index -> IndexError in transform)
+        merge = name != "splat_coarse"
+        types = rng.choice(["A", "B", "C"] if merge else ["A", "B", "A1", "C2"], c["P"]).tolist()
+        write_snapshot(files / f"{name}.xml", xyz, types, L)
+        tr = sb.toolkit.xmltrans.XmlTransformer(files / f"{name}.xml")
+        x = tr.parse_xml(NxNyNz=c["N"], merge=merge)
+        res = sb.toolkit.xmltrans.XmlTransformer.transform(x, r_cut=c["r_cut"])
+        mine = splat_np.transform(x.data[["x", "y", "z"]].values, x.data["index"].values, len(x.atoms_type), x.NxNyNz, x.lxlylz, c["r_cut"])
+        assert np.array_equal(mine, res.phi), name
+        np.savez_compressed(OUT / f"{name}.npz", phi=res.phi, NxNyNz=x.NxNyNz, lxlylz=x.lxlylz, r_cut=c["r_cut"],
+                            index=x.data["index"].values, xyz=x.data[["x", "y", "z"]].values, atoms_type=np.array(x.atoms_type), merge=merge)
+        print(f"  {name}: N {x.NxNyNz} types {x.atoms_type} total {res.phi.sum():.0f}")
+
+
 def main():
     if not ref_live.available():
         sys.exit("live reference not present; goldens can only be generated in the build container")
@@ -215,6 +255,7 @@ def main():
     print("scatter:"); gen_scatter()
     print("voronoi:"); gen_voronoi()
     print("reader:"); gen_reader()
+    print("splat:"); gen_splat()
 
 
 if __name__ == "__main__":

@@ -6,14 +6,15 @@ Drop-in for the corresponding SimuBox entry points (same names and signatures):
 ``libsimubox_b200.so`` (hand-written sm_100a CUDA + cuFFT); there is no CPU fallback.
 """
 from .schema import (AnalyzeMode, ColorMode, Density, DensityParseResult, OpenCVResult, Printout,
-                     ScatterPlot, ScatterResult, WeightedMode)
+                     ScatterPlot, ScatterResult, WeightedMode, XML, XMLTransResult)
 from .reader import check_filepath, parse_density, read_density, read_printout
 from .peak import gaussian_expansion
 from .scatter import Scatter
 from .voronoi import VoronoiCell
+from .xmltrans import XmlTransformer, splat_particles
 
 __all__ = [
     "AnalyzeMode", "ColorMode", "Density", "DensityParseResult", "OpenCVResult", "Printout", "ScatterPlot",
     "ScatterResult", "WeightedMode", "check_filepath", "parse_density", "read_density", "read_printout",
-    "gaussian_expansion", "Scatter", "VoronoiCell",
+    "gaussian_expansion", "Scatter", "VoronoiCell", "XML", "XMLTransResult", "XmlTransformer", "splat_particles",
 ]

@@ -9,7 +9,7 @@ from pathlib import Path
 PKG = Path(__file__).resolve().parent
 CSRC = PKG / "csrc"
 LIB = PKG / "libsimubox_b200.so"
-SOURCES = ["scatter.cu", "voronoi.cu", "shell_table.cpp", "slab.cu", "text_table.cpp", "cellstats.cu", "seeds.cu"]
+SOURCES = ["scatter.cu", "voronoi.cu", "shell_table.cpp", "slab.cu", "text_table.cpp", "cellstats.cu", "seeds.cu", "splat.cu"]
 
 
 def nvcc_path() -> str:

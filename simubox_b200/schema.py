@@ -127,3 +127,30 @@ class OpenCVResult(MixinBaseModel):
     parsed_density: DensityParseResult
     facets: Sequence
     centers: np.ndarray
+
+
+class XML(MixinBaseModel):
+    """Parsed particle snapshot (reference DataFile.py:175-182)."""
+    path: Path
+    NxNyNz: np.ndarray
+    lxlylz: np.ndarray
+    grid_spacing: np.ndarray
+    data: pd.DataFrame
+    atoms_type: list
+    atoms_mapping: dict[str, int]
+
+
+class XMLTransResult(MixinBaseModel):
+    """Densities splatted from a particle snapshot (reference DataFile.py:185-221)."""
+    xml: XML
+    phi: np.ndarray
+
+    def write(self, phi: Optional[np.ndarray] = None, path: Optional[Union[str, Path]] = None, scale: bool = False):
+        """One row per grid point, one column per type, ``Nx Ny Nz`` header -- a phin-style file."""
+        phi = self.phi if phi is None else phi
+        if scale:
+            phi = phi / phi.sum(axis=0)
+        table = np.stack([np.asarray(p).reshape(-1) for p in phi], axis=1)
+        if path is None:
+            path = self.xml.path.with_suffix(".txt")
+        np.savetxt(path, table, fmt="%.3f", delimiter=" ", header=" ".join(map(str, self.xml.NxNyNz)), comments="")
