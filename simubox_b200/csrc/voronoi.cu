@@ -21,6 +21,8 @@
 // fall back to a generic per-voxel evaluation of all three images per axis.
 #include <cstdint>
 #include <cstdlib>
+#include <type_traits>
+#include <cstdlib>
 #include <cuda_runtime.h>
 #include <new>
 
@@ -421,12 +423,13 @@ __device__ __noinline__ bool sqrt_less(double a, double b) { return __dsqrt_rn(a
 template <int ND> struct WarpTile;
 template <> struct WarpTile<3> {
   static constexpr int M0 = 16, M1 = 16, M2 = 16, W0 = 4, W1 = 8;
-  __device__ static void origin(int warp, int half, int o[3]) { o[0] = (warp & 3) * 4; o[1] = (warp >> 2) * 8; o[2] = half * 8; }
+  // gw = 0..15: the warp's number within the mid tile
+  __device__ static void origin(int gw, int o[3]) { o[0] = (gw & 3) * 4; o[1] = ((gw >> 2) & 1) * 8; o[2] = (gw >> 3) * 8; }
   __device__ static void lane_xy(int lane, int& lx, int& ly) { lx = lane >> 3; ly = lane & 7; }
 };
 template <> struct WarpTile<2> {
   static constexpr int M0 = 1, M1 = 64, M2 = 64, W0 = 1, W1 = 32;
-  __device__ static void origin(int warp, int half, int o[3]) { o[0] = 0; o[1] = (warp & 1) * 32; o[2] = half * 32 + (warp >> 1) * 8; }
+  __device__ static void origin(int gw, int o[3]) { o[0] = 0; o[1] = (gw & 1) * 32; o[2] = (gw >> 1) * 8; }
   __device__ static void lane_xy(int lane, int& lx, int& ly) { lx = 0; ly = lane; }
 };
 
@@ -434,8 +437,12 @@ template <> struct WarpTile<2> {
 // compare sums of squares and take the square root only when the two sums are within 8 ulps, where
 // rounding of the root could turn "smaller" into "equal" (then the lower index keeps the voxel, like
 // argmin).  MODE 2: additive with weights -- interval pruning, sqrt(ss) - w per candidate.
-template <int ND, int MODE>
-__global__ void __launch_bounds__(256, 3)
+// W warps per CTA (a mid tile = 16 warp tiles = 16 / W CTAs): warps finish at very different times (a tile inside
+// one cell keeps a single candidate), and a CTA's slot is only recycled when its slowest warp is done.
+// Each warp works through R warp tiles of the same mid tile one after the other (no barrier in between: the staged
+// records are read-only), so the staging, the barrier and the TMA wait are paid once per R * W warp tiles.
+template <int ND, int MODE, int W, int R>
+__global__ void __launch_bounds__(32 * W, 24 / W)
 label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restrict__ weights,
              const SeedRec* __restrict__ rec, const int* __restrict__ ridx, const int* __restrict__ rcount,
              const int* __restrict__ clist, const int* __restrict__ ccount, const uint8_t* __restrict__ mask,
@@ -443,26 +450,17 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
   using WT = WarpTile<ND>;
   __shared__ alignas(128) SeedRec s_rec[kCap];
   __shared__ alignas(16) int s_idx[kCap];
-  __shared__ alignas(16) double s_dz[8][32];      // per warp: (z_c - z_k)^2 of a batch of 4 candidates x 8 voxels
-  __shared__ unsigned char s_list[8][kCap];       // per warp: surviving record slots, ascending
+  __shared__ alignas(16) double s_dz[W][32];      // per warp: (z_c - z_k)^2 of a batch of 4 candidates x 8 voxels
+  __shared__ unsigned char s_list[W][kCap];       // per warp: surviving record slots, ascending
   __shared__ alignas(8) uint64_t s_bar;
-  // grid = (2 * nm[2], nm[1], nm[0]): no integer division to find the tile
-  const int t[3] = {(int)blockIdx.z, (int)blockIdx.y, (int)(blockIdx.x >> 1)};
-  const int half = blockIdx.x & 1;
+  // grid = (kParts * nm[2], nm[1], nm[0]): no integer division to find the tile
+  constexpr int kParts = 16 / (W * R);
+  const int t[3] = {(int)blockIdx.z, (int)blockIdx.y, (int)(blockIdx.x / kParts)};
+  const int part = blockIdx.x % kParts;
   const int tile = (t[0] * g.nm[1] + t[1]) * g.nm[2] + t[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  int o[3], lx, ly;
-  WT::origin(warp, half, o);
+  int lx, ly;
   WT::lane_xy(lane, lx, ly);
-  const int x0 = t[0] * WT::M0 + o[0], y0 = t[1] * WT::M1 + o[1], z0 = t[2] * WT::M2 + o[2];
-  const bool w_in = x0 < g.N[0] && y0 < g.N[1] && z0 < g.N[2];
-  const int vx = x0 + lx, vy = y0 + ly;
-  const bool col_in = w_in && vx < g.N[0] && vy < g.N[1];
-  const int nz = min(kCol, g.N[2] - z0);
-  const long long lin = ((long long)vx * g.N[1] + vy) * g.N[2] + z0;
-  const bool mfast = mask && col_in && nz == kCol && (reinterpret_cast<uintptr_t>(mask + lin) & 7) == 0;
-  uint2 mraw = make_uint2(0u, 0u);
-  if (mfast) mraw = __ldg(reinterpret_cast<const uint2*>(mask + lin));  // issued first: the longest latency of the CTA
   const int raw = rcount[tile];
   const int count = raw & (kFlagGeneric - 1);
   const bool generic = MODE == 0 || (raw & kFlagGeneric) != 0;
@@ -476,8 +474,22 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
     tma_bulk_g2s(s_rec, rec + (long long)tile * kCap, b_rec, &s_bar);
     tma_bulk_g2s(s_idx, ridx + (long long)tile * kCap, b_idx, &s_bar);
   }
-
-  if (!w_in) return;  // whole warp outside the grid (no CTA barrier follows)
+  unsigned long long evals = 0;
+  bool waited = false;
+#pragma unroll 1
+  for (int round = 0; round < R; ++round) {
+  int o[3];
+  WT::origin((part * R + round) * W + warp, o);
+  const int x0 = t[0] * WT::M0 + o[0], y0 = t[1] * WT::M1 + o[1], z0 = t[2] * WT::M2 + o[2];
+  const bool w_in = x0 < g.N[0] && y0 < g.N[1] && z0 < g.N[2];
+  const int vx = x0 + lx, vy = y0 + ly;
+  const bool col_in = w_in && vx < g.N[0] && vy < g.N[1];
+  const int nz = min(kCol, g.N[2] - z0);
+  const long long lin = ((long long)vx * g.N[1] + vy) * g.N[2] + z0;
+  const bool mfast = mask && col_in && nz == kCol && (reinterpret_cast<uintptr_t>(mask + lin) & 7) == 0;
+  uint2 mraw = make_uint2(0u, 0u);
+  if (mfast) mraw = __ldg(reinterpret_cast<const uint2*>(mask + lin));  // issued first: the longest latency of the round
+  if (!w_in) continue;  // whole warp outside the grid (no CTA barrier follows)
   unsigned live = col_in ? (1u << nz) - 1u : 0u;
   if (mask && col_in) {
     live = 0;
@@ -496,9 +508,11 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
   int bi[kCol];
 #pragma unroll
   for (int k = 0; k < kCol; ++k) bi[k] = -1;
-  unsigned long long evals = 0;
 
-  if (staged) mbar_wait(&s_bar, 0);
+  if (staged && !waited) {
+    mbar_wait(&s_bar, 0);
+    waited = true;
+  }
   if (any_live) {
     if (!staged || generic) {
       // generic path: every thread scans the candidate set with the three-image expression
@@ -628,7 +642,7 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
         }
         __syncwarp();
       }
-      evals = (unsigned long long)kept * (unsigned long long)__popc(live);
+      evals += (unsigned long long)kept * (unsigned long long)__popc(live);
     }
   }
   if (col_in) {
@@ -643,11 +657,12 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
       for (int k = 0; k < nz; ++k) labels[lin + k] = (live >> k & 1u) ? bi[k] : -1;
     }
   }
+  }  // rounds
   if (stats) {
 #pragma unroll
     for (int off = 16; off > 0; off >>= 1) evals += __shfl_xor_sync(kFull, evals, off);
     if (lane == 0 && evals) atomicAdd(&stats[0], evals);
-    if (tid == 0 && half == 0) {
+    if (tid == 0 && part == 0) {
       atomicAdd(&stats[1], 1ull);
       if (!staged) atomicAdd(&stats[2], 1ull);
     }
@@ -664,13 +679,30 @@ static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, c
                            int32_t* labels, unsigned long long* stats, cudaStream_t st) {
   coarse_kernel<ND><<<(unsigned)ctiles, 256, 0, st>>>(g, seeds, weights, clist, ccount);
   mid_kernel<ND><<<(unsigned)((tiles + 3) / 4), 128, 0, st>>>(g, (int)tiles, seeds, weights, clist, ccount, rec, ridx, rcount);
-  const dim3 lgrid((unsigned)(2 * g.nm[2]), (unsigned)g.nm[1], (unsigned)g.nm[0]);
-  if (g.mode == 1)
-    label_kernel<ND, 0><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
-  else if (!weights)
-    label_kernel<ND, 1><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
-  else
-    label_kernel<ND, 2><<<lgrid, 256, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+  // (warps per CTA, warp tiles per warp).  Measured at 256^3 / 4096 seeds: (8,1) 0.124 ms, (4,1) 0.110 ms, (4,2) 0.118,
+  // (4,4) 0.121, (2,8) 0.126: small CTAs recycle their SM slot sooner; more rounds per warp cost registers.
+  static const int lw = [] { const char* e = getenv("SBX_LABEL_WARPS"); const int v = e ? atoi(e) : 4; return v == 2 || v == 8 ? v : 4; }();
+  static const int lr = [] { const char* e = getenv("SBX_LABEL_ROUNDS"); return e ? atoi(e) : 1; }();
+  auto launch_label = [&](auto mode_tag) {
+    constexpr int MODE = decltype(mode_tag)::value;
+    auto go = [&](auto w_tag, auto r_tag) {
+      constexpr int W = decltype(w_tag)::value, R = decltype(r_tag)::value;
+      const dim3 lgrid((unsigned)((16 / (W * R)) * g.nm[2]), (unsigned)g.nm[1], (unsigned)g.nm[0]);
+      label_kernel<ND, MODE, W, R><<<lgrid, 32 * W, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+    };
+    using I1 = std::integral_constant<int, 1>;
+    using I2 = std::integral_constant<int, 2>;
+    using I4 = std::integral_constant<int, 4>;
+    using I8 = std::integral_constant<int, 8>;
+    if (lw == 8) go(I8{}, I1{});
+    else if (lw == 2) go(I2{}, I8{});
+    else if (lr == 1) go(I4{}, I1{});
+    else if (lr == 2) go(I4{}, I2{});
+    else go(I4{}, I4{});
+  };
+  if (g.mode == 1) launch_label(std::integral_constant<int, 0>{});
+  else if (!weights) launch_label(std::integral_constant<int, 1>{});
+  else launch_label(std::integral_constant<int, 2>{});
 }
 
 // A plan owns the per-grid workspace (candidate lists of the coarse and mid tiles), so that repeated
