@@ -470,23 +470,75 @@ def run_slab(args):
         return
     peak, peak_src = measured_peak_gbs()
     spec = 16 * n * n * (n // 2 + 1)
-    # per field: read the field, write + read the half spectrum twice (2D stage, exchange buffers, 1D stage), scan it
-    bytes_field = 8 * n ** 3 + 6 * spec
+    pruned = slab.path == 4
+    # pruned DFT: the field is read once.  slab FFT: field + write/read of the half spectrum through the 2D stage,
+    # the exchange buffers and the 1D stage, then the scan
+    bytes_field = 8 * n ** 3 if pruned else 8 * n ** 3 + 6 * spec
+    kern = "pruned_blocked_kernel" if pruned else "cuFFT 2D + slab_pack_kernel + cuFFT 1D + shell_histogram_kernel"
+    comm = "all-reduce of the mode sums (no all-to-all)" if pruned else "NCCL all-to-all (send/recv group) + all-reduce"
     print(json.dumps({
         "metric": "density fields/sec (I(q), one slab-decomposed field)", "value": 1.0 / (ms * 1e-3), "unit": "fields/s",
         "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
         "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": f"one {n}^3 fp64 field, {world} slab(s) of {hi - lo} planes, cutoff=30", "grid": [n, n, n],
                    "l2": f"{8 * n ** 3 / world / 1e9:.1f} GB per rank per pass exceed the 126 MB L2",
-                   "parallelism": f"slab decomposition over {world} rank(s): NCCL all-to-all (send/recv group) + all-reduce"},
+                   "path": "pruned_dft_blocked" if pruned else "slab_fft", "parallelism": f"slab decomposition over {world} rank(s): {comm}"},
         "stage_ms": prof, "n_shells": int(slab.n_shells), "dc_row": float(I[0]),
-        "roofline": {"bound": "hbm", "kernel": "cuFFT 2D + slab_pack_kernel + cuFFT 1D + shell_histogram_kernel",
+        "roofline": {"bound": "hbm", "kernel": kern,
                      "achieved": bytes_field / world / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
                      "frac": bytes_field / world / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_field": bytes_field},
-        "gpu_launches": 2 * args.steps, "clocks": clk.summary(),
+        "gpu_launches": (3 if pruned else 2) * args.steps, "clocks": clk.summary(),
     }))
     slab.close()
+
+
+# ----------------------------------------------------------------------------- phase-diagram sweep (config 4)
+def run_sweep(args):
+    """BASELINE config 4: a sweep of 256^3 fields sharded over the GPUs; per field scatter I(q)+peaks AND periodic
+    Voronoi labelling of its masked grid with 4096 domain-centre seeds.  --fields = fields per GPU (weak scaling)."""
+    import torch
+
+    from simubox_b200 import Scatter, VoronoiCell, synth
+
+    rank, world, local = dist_setup(args.gpus)
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    n, cells, B = args.vgrid, 4, args.fields
+    shape, L = (n, n, n), synth.box_for(cells)
+    fields = torch.empty((B, *shape), dtype=torch.float64, device=dev)
+    masks = torch.empty((B, *shape), dtype=torch.uint8, device=dev)
+    for b in range(B):
+        fields[b] = synth.fields_torch(rank * B + b, 1, shape, cells=cells, device=dev)[0]
+        masks[b] = (fields[b] > 0.5).to(torch.uint8)
+    seeds = [torch.from_numpy(synth.seeds_lattice(shape, 16, 4.0, 77 + rank * B + b)).to(dev) for b in range(min(B, 16))]
+    kw = dict(cutoff=30, threshold=1e-12, peaks=True, width=PEAK_KW["width"], step=PEAK_KW["step"], peak_cutoff=PEAK_KW["cutoff"],
+              min_height=PEAK_KW["min_height"], max_batch=min(32, B), device=local)
+    box = (float(n),) * 3
+    last = {}
+
+    def step():
+        last["scatter"] = Scatter.sacttering_peak_batch(fields, L, **kw)
+        for b in range(B):
+            last["lab"] = VoronoiCell.label_grid(seeds[b % len(seeds)], 0, shape=shape, box=box, mask=masks[b], device=local, return_tensor=True)
+
+    with ClockSampler(local) as clk:
+        ms = timed_steps(step, args.steps, args.warmup, world, dev)
+    if rank != 0:
+        return
+    peak, peak_src = measured_peak_gbs()
+    bytes_field = 8 * n ** 3 + (4 * n ** 3 + 32 * 4096 + n ** 3)  # field read once + labels, seeds, mask
+    print(json.dumps({
+        "metric": "sweep fields/sec (I(q)+peaks and Voronoi labelling per field)", "value": B * world / (ms * 1e-3), "unit": "fields/s",
+        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": f"{B} synthetic {n}^3 fields per GPU: scatter cutoff=30 + show_peak, and periodic Voronoi labels (4096 seeds, uint8 mask) per field",
+                   "l2": f"{B * 8 * n ** 3 / 1e9:.1f} GB of fields per pass exceed the 126 MB L2", "parallelism": f"fields sharded, {world} rank(s), no collective"},
+        "roofline": {"bound": "hbm", "kernel": "pruned_ring_kernel + coarse/mid/label kernels", "achieved": bytes_field * B / (ms * 1e-3) / 1e9,
+                     "peak": peak, "unit": "GB/s", "frac": bytes_field * B / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                     "algorithmic_bytes_per_field": bytes_field},
+        "gpu_launches": args.steps * (-(-B // min(32, B)) + 3 * B), "clocks": clk.summary(),
+    }))
 
 
 # ----------------------------------------------------------------------------- reference arm
@@ -529,7 +581,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--workload", default="scatter", choices=["scatter", "voronoi", "slab"])
+    ap.add_argument("--workload", default="scatter", choices=["scatter", "voronoi", "slab", "sweep"])
     ap.add_argument("--path", default="auto", choices=["auto", "dense", "gather", "pruned", "fused"])
     ap.add_argument("--grid", type=int, default=128)
     ap.add_argument("--cells", type=int, default=2)
@@ -552,6 +604,8 @@ def main():
         run_voronoi(args)
     elif args.workload == "slab":
         run_slab(args)
+    elif args.workload == "sweep":
+        run_sweep(args)
     else:
         run_scatter(args)
     if int(os.environ.get("WORLD_SIZE", "1")) > 1:

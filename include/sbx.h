@@ -175,6 +175,10 @@ int sbx_scatter_slab_execute(sbx_slab_plan* plan, const double* local_slab, doub
                              void* stream);
 /* stage timing of the last execute after set_profiling(1): ms4_host = [2D FFT + pack, all-to-all,
  * 1D FFT, histogram + all-reduce]; synchronises on the last event */
+/* SBX_SCATTER_PRUNED_FUSED when the plan runs the pruned DFT (every shell mode low: each rank reduces its planes
+ * to the mode sums, one small all-reduce, no all-to-all), SBX_SCATTER_FFT_DENSE for the slab FFT.  The
+ * environment variable SBX_SLAB_PATH=fft|pruned forces one at plan creation. */
+int sbx_scatter_slab_path(const sbx_slab_plan* plan);
 int sbx_scatter_slab_set_profiling(sbx_slab_plan* plan, int enable);
 int sbx_scatter_slab_profile(sbx_slab_plan* plan, double* ms4_host);
 int sbx_scatter_slab_plan_destroy(sbx_slab_plan* plan);

@@ -41,7 +41,13 @@ struct FusedArgs {
   const int* shell_off;
   int n_shells;
   double factor;
-  int xc, chunks;     // planes per unit, units per field
+  int xc, chunks;     // planes per unit, plane chunks per field
+  int parts;          // units per field: chunks (x yblocks in the blocked kernel)
+  // blocked ("giant grid" / slab) kernel only:
+  int planes;         // x-planes of each field held in `fields` (N0, or this rank's slab)
+  int x_base;         // global x index of the first of them
+  int yb_rows, yblocks;  // a unit covers yb_rows rows of its planes; N1 = yb_rows * yblocks
+  int finish;         // 0: leave the partial sums (they are reduced across ranks first)
   double2* partial;   // [n_fields][chunks][n_umodes]
   unsigned* ctrl;     // [0] unit counter, [1 + field] tickets (zeroed before the launch)
   int work_doubles;   // size of the per-CTA scratch region
@@ -70,10 +76,10 @@ __device__ inline void fused_finish(const FusedArgs& A, int field, double* work)
   double* row = work;              // n_shells
   double* Iu = work + A.n_shells;  // n_umodes (region reused by the peak search afterwards)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
-  const double2* part = A.partial + (long long)field * A.chunks * A.n_umodes;
+  const double2* part = A.partial + (long long)field * A.parts * A.n_umodes;
   for (int u = tid; u < A.n_umodes; u += blockDim.x) {
     double sr = 0.0, si = 0.0;
-    for (int ch = 0; ch < A.chunks; ++ch) {  // fixed order: independent of which CTA produced which unit
+    for (int ch = 0; ch < A.parts; ++ch) {  // fixed order: independent of which CTA produced which unit
       const double2 p = __ldcg(part + (long long)ch * A.n_umodes + u);
       sr += p.x;
       si += p.y;
@@ -214,6 +220,158 @@ pruned_fused_kernel(const FusedArgs A) {
     }
     __syncthreads();  // work / s_unit are reused by the next unit
   }
+}
+
+// ------------------------------------------------------------------------------------------
+// Blocked variant for grids whose planes do not fit the scheme above (512^3, 1024^3) and for slabs of
+// one field spread over several GPUs.  Same stages; differences:
+//  * a unit = xc planes x ONE block of yb_rows rows, so the stage-1 buffer is 16 x (yb_rows + 4) whatever N1
+//    is; the y transform of a block uses the block's slice of the twiddle table and its 16 x 16 result goes
+//    straight through the (linear) x stage -- partial sums simply have more terms;
+//  * z and y twiddles are read through L1 (__ldg) instead of being copied to shared memory (64 KB +
+//    128 KB at 1024^3), leaving room for 3 CTAs per SM;
+//  * `planes` / `x_base`: the field pointer holds only this rank's planes, the x twiddle uses the global
+//    plane index; `finish = 0` stops after the partial sums (summed over ranks before the shell sums).
+__host__ __device__ inline size_t blocked_work_doubles(int yb_rows, int n_shells, int n_umodes, int step, bool peaks) {
+  const size_t a = (size_t)16 * (yb_rows + 4) + 512;
+  const size_t b = (size_t)n_shells + n_umodes + 2 + (peaks ? (size_t)step + 2 * (size_t)n_shells : 0);
+  return a > b ? a : b;
+}
+__host__ __device__ inline size_t blocked_smem_bytes(int N0, size_t work_doubles) {
+  return (2 * (size_t)N0 + work_doubles) * sizeof(double);
+}
+
+__global__ void __launch_bounds__(256, 3)
+pruned_blocked_kernel(const FusedArgs A) {
+  extern __shared__ double sm[];
+  double2* tw0 = reinterpret_cast<double2*>(sm);      // N0
+  double* work = reinterpret_cast<double*>(tw0 + A.N0);
+  const int gstride = A.yb_rows + 4;
+  double* gT = work;                                  // 16 * gstride
+  double* c2 = gT + (size_t)16 * gstride;             // 256
+  double* hp = c2 + 256;                              // 256
+  __shared__ int s_unit, s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < A.N0; i += 256) tw0[i] = A.tw0[i];
+  int4 md[kFusedModesPerThread];
+  int orc[kFusedModesPerThread];
+#pragma unroll
+  for (int k = 0; k < kFusedModesPerThread; ++k) {
+    const int u = tid + 256 * k;
+    md[k] = u < A.n_umodes ? A.umodes[u] : make_int4(0, 0, 0, 0);
+    orc[k] = md[k].z * 16 + (md[k].y < 0 ? -md[k].y : md[k].y);
+  }
+  const int m = lane >> 2, kk = lane & 3;
+  const int groups = A.yb_rows >> 3, ksb = A.yb_rows >> 2;
+  const int n_units = A.n_fields * A.parts;
+  const long long plane_doubles = (long long)A.N1 * A.N2;
+  const int n0 = 2 * kk, n1 = 2 * kk + 1;
+  const int re0 = n0 < 4 ? 2 * n0 : 8 + 2 * (n0 - 4), re1 = n1 < 4 ? 2 * n1 : 8 + 2 * (n1 - 4);
+  __syncthreads();
+
+  for (;;) {
+    if (tid == 0) s_unit = (int)atomicAdd(&A.ctrl[0], 1u);
+    __syncthreads();
+    const int unit = s_unit;
+    if (unit >= n_units) break;
+    const int field = unit / A.parts, part = unit - field * A.parts;
+    const int chunk = part / A.yblocks, yb = part - chunk * A.yblocks;
+    const int x0 = chunk * A.xc;
+    double fr[kFusedModesPerThread], fi[kFusedModesPerThread];
+    int jj[kFusedModesPerThread];
+#pragma unroll
+    for (int k = 0; k < kFusedModesPerThread; ++k) {
+      fr[k] = 0.0; fi[k] = 0.0;
+      jj[k] = (int)(((long long)md[k].x * (A.x_base + x0)) % A.N0);
+    }
+    for (int x = x0; x < x0 + A.xc; ++x) {
+      const double* base = A.fields + ((long long)field * A.planes + x) * plane_doubles + (long long)yb * A.yb_rows * A.N2;
+      // ---- stage 1 (z, folded): each warp transforms 8 rows at a time
+      for (int grp = warp; grp < groups; grp += 8) {
+        const double2* row = reinterpret_cast<const double2*>(base + (long long)(grp * 8 + m) * A.N2) + kk;
+        const double2* row2 = row + (A.N2 >> 2);
+        double e0 = 0.0, e1 = 0.0, o0 = 0.0, o1 = 0.0;
+#pragma unroll 4
+        for (int s = 0; s < A.ds; ++s) {
+          const double2 a = __ldg(row + 4 * s), b = __ldg(row2 + 4 * s);
+          const double* tw = A.twf + s * 128 + lane;
+          dmma_m8n8k4(e0, e1, a.x + b.x, __ldg(tw));
+          dmma_m8n8k4(e0, e1, a.y + b.y, __ldg(tw + 32));
+          dmma_m8n8k4(o0, o1, a.x - b.x, __ldg(tw + 64));
+          dmma_m8n8k4(o0, o1, a.y - b.y, __ldg(tw + 96));
+        }
+        const int y = grp * 8 + m;
+        gT[(size_t)re0 * gstride + y] = e0;
+        gT[(size_t)re1 * gstride + y] = e1;
+        gT[(size_t)(re0 + 1) * gstride + y] = o0;
+        gT[(size_t)(re1 + 1) * gstride + y] = o1;
+      }
+      __syncthreads();
+      // ---- stage 2 (y): 16 x 16 x yb_rows product with this block's slice of the twiddles
+      {
+        const int mt = warp & 1, nt = (warp >> 1) & 1, kh = warp >> 2;
+        const int s0 = kh * (ksb >> 1), s1 = s0 + (ksb >> 1);
+        const double* arow = gT + (size_t)(8 * mt + m) * gstride;
+        const double* brow = A.tw1 + ((size_t)nt * A.ks1 + (size_t)yb * ksb) * 32;
+        double d0 = 0.0, d1 = 0.0;
+#pragma unroll 4
+        for (int s = s0; s < s1; ++s) dmma_m8n8k4(d0, d1, arow[4 * s + kk], __ldg(brow + s * 32 + lane));
+        const int r = 8 * mt + m, c = 8 * nt + 2 * kk;
+        if (kh == 1) { c2[r * 16 + c] = d0; c2[r * 16 + c + 1] = d1; }
+        __syncthreads();
+        if (kh == 0) { hp[r * 16 + c] = d0 + c2[r * 16 + c]; hp[r * 16 + c + 1] = d1 + c2[r * 16 + c + 1]; }
+      }
+      __syncthreads();
+      // ---- stage 3 (x)
+#pragma unroll
+      for (int k = 0; k < kFusedModesPerThread; ++k) {
+        if (tid + 256 * k < A.n_umodes) {
+          const double rc = hp[orc[k]], rs = hp[orc[k] + 8], sc = hp[orc[k] + 128], ss = hp[orc[k] + 136];
+          const double hr = md[k].y >= 0 ? rc - ss : rc + ss;
+          const double hi = md[k].y >= 0 ? -(rs + sc) : rs - sc;
+          const double2 w = tw0[jj[k]];
+          fr[k] += hr * w.x + hi * w.y;
+          fi[k] += hi * w.x - hr * w.y;
+          jj[k] += md[k].x;
+          if (jj[k] >= A.N0) jj[k] -= A.N0;
+        }
+      }
+    }
+    double2* part_out = A.partial + (long long)unit * A.n_umodes;
+#pragma unroll
+    for (int k = 0; k < kFusedModesPerThread; ++k)
+      if (tid + 256 * k < A.n_umodes) part_out[tid + 256 * k] = make_double2(fr[k], fi[k]);
+    if (A.finish) {
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) s_last = atomicAdd(&A.ctrl[1 + field], 1u) == (unsigned)(A.parts - 1);
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        fused_finish(A, field, work);
+      }
+    }
+    __syncthreads();
+  }
+}
+
+// slab path: sums[mode] = sum over this rank's units in fixed order (one thread per mode)
+__global__ void fused_reduce_parts_kernel(const double2* __restrict__ partial, int parts, int n_umodes, double2* __restrict__ sums) {
+  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  if (u >= n_umodes) return;
+  double sr = 0.0, si = 0.0;
+  for (int p = 0; p < parts; ++p) {
+    const double2 v = partial[(long long)p * n_umodes + u];
+    sr += v.x;
+    si += v.y;
+  }
+  sums[u] = make_double2(sr, si);
+}
+
+// slab path: shell sums (+ peaks) from mode sums that are already complete (A.partial = sums, A.parts = 1)
+__global__ void __launch_bounds__(256) fused_finish_kernel(const FusedArgs A) {
+  extern __shared__ double sm[];
+  fused_finish(A, 0, sm);
 }
 
 // ------------------------------------------------------------------------------------------

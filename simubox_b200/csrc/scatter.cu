@@ -101,7 +101,11 @@ struct sbx_scatter_plan {
   int n_umodes = 0;
   bool pruned_ok = false;
   // fused single-kernel variant (pruned_fused.cuh)
-  bool fused_ok = false;
+  bool fused_ok = false;    // whole planes fit the shared-memory scheme of pruned_fused_kernel / pruned_ring_kernel
+  bool modes_ok = false;    // every listed mode lies in the 8 x 8 (k_y, k_z) tile: tables below are built
+  bool blocked_ok = false;  // pruned_blocked_kernel applies (any N1 = yb_rows * yblocks)
+  int yb_rows = 0, yblocks = 1;
+  double2* d_modesum = nullptr;  // slab path: this rank's / the reduced mode sums
   const char* last_kernel = "";  // dominant hand-written kernel of the last execute (bench roofline)
   double* d_twf = nullptr;
   double2* d_partial = nullptr;
@@ -232,7 +236,7 @@ static int build_pruned_tables(sbx_scatter_plan* p) {
   if (t.ndim != 3) return SBX_OK;
   const int64_t N0 = t.N[0], N1 = t.N[1], N2 = t.N[2];
   if (N1 % 8 || N1 < 16 || N2 < 16) return SBX_OK;
-  if (pruned_smem_bytes((int)N1, (int)N2) > 100 * 1024) return SBX_OK;
+  const bool planes_ok = pruned_smem_bytes((int)N1, (int)N2) <= 100 * 1024;  // two-kernel path only
   if (t.n_members() > (int64_t)1 << 16) return SBX_OK;
   std::map<std::array<int64_t, 3>, int> index;
   std::vector<int4> umodes;
@@ -313,6 +317,12 @@ static int build_pruned_tables(sbx_scatter_plan* p) {
     }
     const size_t work = fused_work_doubles((int)N1, t.n_shells(), (int)umodes.size(), 2000, true);
     p->fused_ok = fused_smem_bytes((int)N0, (int)N1, (int)N2, work) <= 200 * 1024;
+    // blocked kernel: blocks of 128 rows (or the whole plane when N1 is small)
+    p->yb_rows = N1 % 128 == 0 ? 128 : (N1 <= 256 ? (int)N1 : 0);
+    if (p->yb_rows) {
+      p->yblocks = (int)(N1 / p->yb_rows);
+      p->blocked_ok = blocked_smem_bytes((int)N0, blocked_work_doubles(p->yb_rows, t.n_shells(), (int)umodes.size(), 2000, true)) <= 200 * 1024;
+    }
   }
   if ((rc = upload(&p->d_tw0, tw0))) return rc;
   if ((rc = upload(&p->d_umodes, umodes))) return rc;
@@ -320,7 +330,8 @@ static int build_pruned_tables(sbx_scatter_plan* p) {
   g.tw2 = p->d_tw2;
   g.tw1 = p->d_tw1;
   p->n_umodes = (int)umodes.size();
-  p->pruned_ok = true;
+  p->modes_ok = true;
+  p->pruned_ok = planes_ok;
   return SBX_OK;
 }
 
@@ -351,7 +362,7 @@ static void free_plan(sbx_scatter_plan* p) {
   cudaFree(p->d_spec);
   cudaFree(p->d_tw2); cudaFree(p->d_tw2f); cudaFree(p->d_tw1); cudaFree(p->d_tw0); cudaFree(p->d_umodes); cudaFree(p->d_memb_u);
   cudaFree(p->d_planes);
-  cudaFree(p->d_twf); cudaFree(p->d_partial); cudaFree(p->d_ctrl);
+  cudaFree(p->d_twf); cudaFree(p->d_partial); cudaFree(p->d_ctrl); cudaFree(p->d_modesum);
   for (int i = 0; i < 2; ++i) {
     cudaFree(p->d_stage[i]); cudaFree(p->d_out[i]); cudaFree(p->d_pidx[i]); cudaFree(p->d_npk[i]);
     if (p->ev_in[i]) cudaEventDestroy(p->ev_in[i]);
@@ -403,7 +414,7 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   const GridDev& g = p->grid;
   if ((rc = build_pruned_tables(p))) { free_plan(p); return rc; }
   if (path == SBX_SCATTER_AUTO) {
-    if (p->pruned_ok && p->fused_ok && !getenv("SBX_NO_PRUNED") && !getenv("SBX_NO_FUSED")) path = SBX_SCATTER_PRUNED_FUSED;
+    if (p->modes_ok && (p->fused_ok || p->blocked_ok) && !getenv("SBX_NO_PRUNED") && !getenv("SBX_NO_FUSED")) path = SBX_SCATTER_PRUNED_FUSED;
     else if (p->pruned_ok && !getenv("SBX_NO_PRUNED")) path = SBX_SCATTER_PRUNED;
     else path = (p->tab.n_members() * 4 <= g.nspec) ? SBX_SCATTER_FFT_GATHER : SBX_SCATTER_FFT_DENSE;
   }
@@ -411,7 +422,7 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
     free_plan(p);
     return fail(SBX_EINVAL, "pruned-DFT path needs a 3D grid (N1 %% 8 == 0, N1,N2 >= 16) whose shell modes have |k_y|,k_z <= 7");
   }
-  if (path == SBX_SCATTER_PRUNED_FUSED && !(p->pruned_ok && p->fused_ok)) {
+  if (path == SBX_SCATTER_PRUNED_FUSED && !(p->modes_ok && (p->fused_ok || p->blocked_ok))) {
     free_plan(p);
     return fail(SBX_EINVAL, "fused pruned-DFT path needs the pruned path's conditions plus N2 %% 16 == 0 and at most %d listed modes", 256 * kFusedModesPerThread);
   }
@@ -449,8 +460,9 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
     }
   }
   else if (path == SBX_SCATTER_PRUNED_FUSED) {
-    const size_t chunks = (size_t)g.N0 / p->fused_xc;
-    e = cudaMalloc((void**)&p->d_partial, (size_t)p->chunk * chunks * std::max(p->n_umodes, 1) * sizeof(double2));
+    const size_t parts = (size_t)g.N0 / p->fused_xc * (p->blocked_ok ? p->yblocks : 1);
+    e = cudaMalloc((void**)&p->d_partial, (size_t)p->chunk * parts * std::max(p->n_umodes, 1) * sizeof(double2));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_modesum, (size_t)std::max(p->n_umodes, 1) * sizeof(double2));
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_ctrl, ((size_t)p->chunk + 1) * sizeof(unsigned));
   }
   else e = cudaMalloc((void**)&p->d_spec, (size_t)p->chunk * g.nspec * sizeof(double2));
@@ -466,6 +478,8 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   cudaFuncSetAttribute(pruned_planes_fullk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(pruned_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(fused_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_ring_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
   cudaFuncSetAttribute(pruned_ring_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
@@ -529,6 +543,8 @@ static int check_peaks_args(int n, int step, int max_peaks) {
   return SBX_OK;
 }
 
+namespace sbx { static int blocked_unit_planes(const sbx_scatter_plan* p, int n_fields, int planes); }
+
 // scatter (+ optional fused peaks) on `batch` device-resident fields
 static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, double* shell_I, bool do_peaks,
                        const PeakParams& pp, double* plot_y, int32_t* peak_idx, int32_t* n_peaks,
@@ -553,6 +569,39 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
     A.xc = p->fused_xc; A.chunks = g.N0 / p->fused_xc;
     A.partial = p->d_partial; A.ctrl = p->d_ctrl;
     A.do_peaks = do_peaks ? 1 : 0; A.q = p->d_q; A.pp = pp;
+    A.parts = A.chunks; A.planes = g.N0; A.x_base = 0; A.yb_rows = g.N1; A.yblocks = 1; A.finish = 1;
+    const char* fb_env = getenv("SBX_FUSED_BLOCKED");  // read per call: the tests switch it
+    const int force_blocked = fb_env ? atoi(fb_env) : 0;
+    // whole-plane kernels need >= 2 CTAs per SM to hide their barriers; beyond that (512^3, 1024^3): row-blocked kernel
+    const bool whole_plane_thin = fused_smem_bytes(g.N0, g.N1, g.N2, fused_work_doubles(g.N1, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks)) > 113 * 1024;
+    if ((!p->fused_ok || force_blocked || whole_plane_thin) && p->blocked_ok) {
+      A.yb_rows = p->yb_rows; A.yblocks = p->yblocks;
+      A.xc = blocked_unit_planes(p, std::min(p->chunk, batch), g.N0);
+      A.chunks = g.N0 / A.xc; A.parts = A.chunks * A.yblocks;
+      const size_t bwork = blocked_work_doubles(p->yb_rows, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks);
+      A.work_doubles = (int)bwork;
+      const size_t bsmem = blocked_smem_bytes(g.N0, bwork);
+      if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
+      p->last_kernel = "pruned_blocked_kernel";
+      for (int c0 = 0; c0 < batch; c0 += p->chunk) {
+        const int nb = std::min(p->chunk, batch - c0);
+        A.fields = fields + (size_t)c0 * g.nreal;
+        A.n_fields = nb;
+        A.shell_I = shell_I + (size_t)c0 * ns;
+        A.plot_y = plot_y ? plot_y + (size_t)c0 * pp.step : nullptr;
+        A.peak_idx = peak_idx ? peak_idx + (size_t)c0 * pp.max_peaks : nullptr;
+        A.n_peaks = n_peaks ? n_peaks + c0 : nullptr;
+        SBX_CUDA(cudaMemsetAsync(p->d_ctrl, 0, ((size_t)nb + 1) * sizeof(unsigned), st));
+        const long long units = (long long)nb * A.parts;
+        const int grid = (int)std::min<long long>(units, (long long)p->pruned_ctas_per_sm * p->sm_count);
+        if (p->profiling) prof_event(p, st);
+        pruned_blocked_kernel<<<grid, 256, bsmem, st>>>(A);
+        SBX_CUDA(cudaGetLastError());
+        if (p->profiling) { prof_event(p, st); prof_event(p, st); }
+        p->own_launches += 1;
+      }
+      return SBX_OK;
+    }
     const size_t work = fused_work_doubles(g.N1, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks);
     A.work_doubles = (int)work;
     const size_t smem = fused_smem_bytes(g.N0, g.N1, g.N2, work);
@@ -725,6 +774,75 @@ extern "C" int sbx_scatter_plan_get_profile(sbx_scatter_plan* plan, double* tran
   }
   return SBX_OK;
 }
+
+// ---- pruned-DFT slab helpers (scatter_types.h) --------------------------------------------------
+namespace sbx {
+
+// planes per unit of the blocked kernel.  Fixed per plan: the summation order, hence the bits of the result, must not
+// depend on how many fields a launch carries.  (Halving it for single-field launches to smooth the last wave was
+// measured slower: 0.62 vs 0.46 ms for one 512^3 field -- the per-unit epilogue outweighs the tail.)
+static int blocked_unit_planes(const sbx_scatter_plan* p, int, int) { return p->fused_xc; }
+
+static void slab_args(const sbx_scatter_plan* p, FusedArgs& A) {
+  const GridDev& g = p->grid;
+  A = FusedArgs{};
+  A.N0 = g.N0; A.N1 = g.N1; A.N2 = g.N2;
+  A.ks1 = g.N1 / 4; A.gstride = g.N1 + 4; A.ds = g.N2 / 16;
+  A.twf = p->d_twf; A.tw1 = p->d_tw1; A.tw0 = p->d_tw0;
+  A.umodes = p->d_umodes; A.n_umodes = p->n_umodes; A.memb_u = p->d_memb_u; A.shell_off = p->d_shell_off;
+  A.n_shells = p->shell.n_shells; A.factor = g.factor;
+  A.xc = p->fused_xc;
+  A.yb_rows = p->yb_rows; A.yblocks = p->yblocks;
+  A.partial = p->d_partial; A.ctrl = p->d_ctrl;
+  A.q = p->d_q;
+}
+
+bool scatter_slab_supported(const sbx_scatter_plan* p, int planes) {
+  return p && p->path == SBX_SCATTER_PRUNED_FUSED && p->blocked_ok && planes >= 1 && planes <= p->grid.N0 && planes % p->fused_xc == 0;
+}
+
+int scatter_slab_n_umodes(const sbx_scatter_plan* p) { return p ? p->n_umodes : 0; }
+
+int scatter_slab_partial(sbx_scatter_plan* p, const double* slab, int planes, int x_base, double2* modesum, cudaStream_t st) {
+  if (!scatter_slab_supported(p, planes)) return fail(SBX_EINVAL, "plan cannot run the pruned slab path on %d planes", planes);
+  if (!slab || !modesum) return fail(SBX_EINVAL, "NULL argument");
+  DeviceGuard guard(p->device);
+  FusedArgs A;
+  slab_args(p, A);
+  A.fields = slab; A.n_fields = 1; A.planes = planes; A.x_base = x_base; A.finish = 0;
+  A.xc = blocked_unit_planes(p, 1, planes);
+  A.chunks = planes / A.xc; A.parts = A.chunks * A.yblocks;
+  const size_t bwork = blocked_work_doubles(p->yb_rows, A.n_shells, p->n_umodes, 0, false);
+  A.work_doubles = (int)bwork;
+  const size_t bsmem = blocked_smem_bytes(A.N0, bwork);
+  if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
+  SBX_CUDA(cudaMemsetAsync(p->d_ctrl, 0, 2 * sizeof(unsigned), st));
+  const int grid = (int)std::min<long long>(A.parts, (long long)p->pruned_ctas_per_sm * p->sm_count);
+  pruned_blocked_kernel<<<grid, 256, bsmem, st>>>(A);
+  SBX_CUDA(cudaGetLastError());
+  fused_reduce_parts_kernel<<<(p->n_umodes + 127) / 128, 128, 0, st>>>(p->d_partial, A.parts, p->n_umodes, modesum);
+  SBX_CUDA(cudaGetLastError());
+  p->own_launches += 2;
+  p->last_kernel = "pruned_blocked_kernel";
+  return SBX_OK;
+}
+
+int scatter_slab_finish(sbx_scatter_plan* p, const double2* modesum, double* shell_I, cudaStream_t st) {
+  if (!p || !modesum || !shell_I) return fail(SBX_EINVAL, "NULL argument");
+  DeviceGuard guard(p->device);
+  FusedArgs A;
+  slab_args(p, A);
+  A.n_fields = 1; A.parts = 1; A.chunks = 1;
+  A.partial = const_cast<double2*>(modesum);
+  A.shell_I = shell_I;
+  const size_t smem = ((size_t)A.n_shells + p->n_umodes + 2) * sizeof(double);
+  fused_finish_kernel<<<1, 256, smem, st>>>(A);
+  SBX_CUDA(cudaGetLastError());
+  p->own_launches += 1;
+  return SBX_OK;
+}
+
+}  // namespace sbx
 
 extern "C" int sbx_scatter_execute(sbx_scatter_plan* plan, const double* fields, int batch, double* shell_I,
                                    void* stream) {

@@ -33,4 +33,16 @@ struct GridDev {
 int launch_shell_histogram3(const double2* spec, const GridDev& g, const ShellDev& sh, double* shell_I,
                             int blocks, cudaStream_t st);
 
+// ---- pruned-DFT slab helpers (defined in scatter.cu; used by slab.cu) --------------------------
+// A plan created with SBX_SCATTER_PRUNED_FUSED can transform `planes` consecutive x-planes of ONE field that start
+// at global plane index x_base: modesum (n_umodes complex sums over those planes, fixed summation order) is what
+// the ranks add up (all-reduce) before scatter_slab_finish turns the totals into the n_shells intensities.
+}  // namespace sbx
+struct sbx_scatter_plan;
+namespace sbx {
+bool scatter_slab_supported(const sbx_scatter_plan* p, int planes);
+int scatter_slab_n_umodes(const sbx_scatter_plan* p);
+int scatter_slab_partial(sbx_scatter_plan* p, const double* slab, int planes, int x_base, double2* modesum, cudaStream_t st);
+int scatter_slab_finish(sbx_scatter_plan* p, const double2* modesum, double* shell_I, cudaStream_t st);
+
 }  // namespace sbx

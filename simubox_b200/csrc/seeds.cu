@@ -58,30 +58,57 @@ __device__ __forceinline__ void unite(int* parent, int a, int b) {
   }
 }
 
+// parent = first voxel of the z-run the voxel belongs to, as far as the warp's 32 consecutive voxels show it (runs
+// are stitched across warp segments and around the box by the merge kernel): most +z unions are done right here
 __global__ void seeds_init_kernel(SeedGeo g, const double* __restrict__ field, double threshold, int* __restrict__ parent) {
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += (long long)gridDim.x * blockDim.x)
-    parent[i] = field[i] > threshold ? (int)i : -1;
+  const int lane = threadIdx.x & 31;
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  const long long n_iter = (g.n + stride - 1) / stride;
+  for (long long it = 0; it < n_iter; ++it) {
+    const long long i = it * stride + (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    const bool in = i < g.n;
+    const bool fg = in && field[i] > threshold;
+    const bool row_start = in && ((unsigned)i % (unsigned)g.N2) == 0;
+    const unsigned f = __ballot_sync(kFull, fg), brk = __ballot_sync(kFull, row_start);
+    if (in) {
+      int p = -1;
+      if (fg) {
+        const unsigned below = (1u << lane) - 1u;
+        const unsigned gaps = ~f & below;                       // background voxels before me
+        const int after_gap = gaps ? 32 - __clz(gaps) : 0;      // first lane after the last gap
+        const unsigned rows = brk & (below | (1u << lane));     // row starts at or before me
+        const int at_row = rows ? 31 - __clz(rows) : 0;
+        p = (int)(i - lane + max(after_gap, at_row));
+      }
+      parent[i] = p;
+    }
+  }
 }
 
 __global__ void seeds_merge_kernel(SeedGeo g, int* parent) {
   const long long plane = (long long)g.N1 * g.N2;
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < g.n; i += (long long)gridDim.x * blockDim.x) {
     if (parent[i] < 0) continue;
-    const int z = (int)(i % g.N2);
-    const long long row = i / g.N2;
-    const int y = (int)(row % g.N1), x = (int)(row / g.N1);
-    // +z, +y, +x neighbours (each face is visited once, from its lower voxel; wrap faces from the last one)
-    if (g.N2 > 1 && (z + 1 < g.N2 || g.periodic)) {
-      const long long j = z + 1 < g.N2 ? i + 1 : i - (g.N2 - 1);
-      if (parent[j] >= 0) unite(parent, (int)i, (int)j);
+    const unsigned ui = (unsigned)i, urow = ui / (unsigned)g.N2;  // n < 2^31: 32-bit divisions
+    const int z = (int)(ui - urow * (unsigned)g.N2);
+    const int x = (int)(urow / (unsigned)g.N1), y = (int)(urow - (unsigned)x * (unsigned)g.N1);
+    // +z: inside a warp segment the init kernel already joined the run; stitch segment ends and the wrap face
+    if (g.N2 > 1) {
+      if (z + 1 < g.N2) {
+        if ((ui & 31u) == 31u && parent[i + 1] >= 0) unite(parent, (int)i, (int)(i + 1));
+      } else if (g.periodic && parent[i - (g.N2 - 1)] >= 0) {
+        unite(parent, (int)i, (int)(i - (g.N2 - 1)));
+      }
     }
+    // +y / +x: the face (i, j) is redundant when the previous voxels of both runs are foreground too
+    // (i ~ i-1, j ~ j-1 along z, and the face (i-1, j-1) is united by the thread of i-1)
     if (g.N1 > 1 && (y + 1 < g.N1 || g.periodic)) {
       const long long j = y + 1 < g.N1 ? i + g.N2 : i - (long long)(g.N1 - 1) * g.N2;
-      if (parent[j] >= 0) unite(parent, (int)i, (int)j);
+      if (parent[j] >= 0 && !(z > 0 && parent[i - 1] >= 0 && parent[j - 1] >= 0)) unite(parent, (int)i, (int)j);
     }
     if (g.N0 > 1 && (x + 1 < g.N0 || g.periodic)) {
       const long long j = x + 1 < g.N0 ? i + plane : i - (long long)(g.N0 - 1) * plane;
-      if (parent[j] >= 0) unite(parent, (int)i, (int)j);
+      if (parent[j] >= 0 && !(z > 0 && parent[i - 1] >= 0 && parent[j - 1] >= 0)) unite(parent, (int)i, (int)j);
     }
   }
 }
@@ -261,9 +288,9 @@ seeds_accumulate_kernel(SeedGeo g, const int* __restrict__ parent, const int* __
           }
           cur = Part{id, 0, 0, 0, 0};
           if (id >= 0) {
-            const long long root = parent[off + k];
-            rx = (int)(root / plane);
-            const int rem = (int)(root - (long long)rx * plane);
+            const unsigned root = (unsigned)parent[off + k];
+            rx = (int)(root / (unsigned)plane);
+            const int rem = (int)(root - (unsigned)rx * (unsigned)plane);
             ry = rem / g.N2;
             rz = rem - ry * g.N2;
           }

@@ -129,6 +129,11 @@ struct sbx_slab_plan {
   int blocks = 1;
   cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};  // stage timing (sbx_scatter_slab_profile)
   bool timed = false;
+  // pruned-DFT mode: no transform of the whole field, no all-to-all -- every rank reduces its planes to the few
+  // hundred low-|q| mode sums the shells need (pruned_blocked_kernel) and the ranks all-reduce those 5 kB
+  bool pruned = false;
+  sbx_scatter_plan* inner = nullptr;
+  double2* d_modesum = nullptr;
 };
 
 static void slab_free(sbx_slab_plan* p) {
@@ -138,6 +143,8 @@ static void slab_free(sbx_slab_plan* p) {
   if (p->have1d) cufftDestroy(p->fft1d);
   cudaFree(p->d_x); cudaFree(p->d_y); cudaFree(p->d_rep); cudaFree(p->d_kvlast); cudaFree(p->d_partial);
   cudaFree(p->d_plane2);
+  cudaFree(p->d_modesum);
+  if (p->inner) sbx_scatter_plan_destroy(p->inner);
   for (cudaEvent_t e : p->ev) if (e) cudaEventDestroy(e);
   delete p;
 }
@@ -163,6 +170,39 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
   p->n1 = (int)(N[1] / world);
   p->H = (int)(N[2] / 2 + 1);
   p->blk = (long long)p->n0 * p->n1 * p->H;
+
+  // ---- mode: pruned DFT when every shell mode is a low one (the default cutoff = 30 case), else slab FFT.
+  // SBX_SLAB_PATH=fft / pruned forces one of them.
+  {
+    const char* sp = getenv("SBX_SLAB_PATH");
+    const bool want_fft = sp && !strcmp(sp, "fft"), want_pruned = sp && !strcmp(sp, "pruned");
+    if (!want_fft) {
+      sbx_scatter_plan* inner = nullptr;
+      if (sbx_scatter_plan_create_ex(&inner, device, 3, N, L, cutoff, threshold, 1, SBX_SCATTER_PRUNED_FUSED) == SBX_OK) {
+        if (scatter_slab_supported(inner, p->n0)) {
+          p->inner = inner;
+          p->pruned = true;
+        } else {
+          sbx_scatter_plan_destroy(inner);
+        }
+      }
+      if (want_pruned && !p->pruned) {
+        slab_free(p);
+        return fail(SBX_EINVAL, "SBX_SLAB_PATH=pruned, but the pruned slab path does not apply to this grid / cutoff / rank count");
+      }
+    }
+    if (p->pruned) {
+      p->shell.n_shells = t.n_shells();
+      cudaError_t e = cudaMalloc((void**)&p->d_modesum, (size_t)std::max(scatter_slab_n_umodes(p->inner), 1) * sizeof(double2));
+      for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&p->ev[i]);
+      if (e != cudaSuccess) {
+        slab_free(p);
+        return fail(SBX_ECUDA, "slab plan allocation: %s", cudaGetErrorString(e));
+      }
+      *out = p;
+      return SBX_OK;
+    }
+  }
 
   // k^2 tables: same construction as the single-GPU plan (scatter.cu build_device_tables)
   GridDev& g = p->grid;
@@ -323,6 +363,16 @@ extern "C" int sbx_scatter_slab_execute(sbx_slab_plan* p, const double* local_sl
   cudaStream_t st = (cudaStream_t)stream;
   int rc;
   if (p->timed) cudaEventRecord(p->ev[0], st);
+  if (p->pruned) {
+    if ((rc = scatter_slab_partial(p->inner, local_slab, p->n0, p->rank * p->n0, p->d_modesum, st))) return rc;
+    if (p->timed) cudaEventRecord(p->ev[1], st);
+    if (p->world > 1)
+      SBX_NCCL(g_nccl.AllReduce(p->d_modesum, p->d_modesum, (size_t)2 * scatter_slab_n_umodes(p->inner), ncclDouble, ncclSum, p->comm, st));
+    if (p->timed) { cudaEventRecord(p->ev[2], st); cudaEventRecord(p->ev[3], st); }
+    if ((rc = scatter_slab_finish(p->inner, p->d_modesum, shell_I, st))) return rc;
+    if (p->timed) cudaEventRecord(p->ev[4], st);
+    return SBX_OK;
+  }
   if ((rc = slab_stage_a(p, local_slab, st))) return rc;
   if (p->timed) cudaEventRecord(p->ev[1], st);
   if (p->world > 1) {
@@ -344,6 +394,11 @@ extern "C" int sbx_scatter_slab_execute(sbx_slab_plan* p, const double* local_sl
   else SBX_CUDA(cudaMemcpyAsync(shell_I, p->d_partial, (size_t)ns * sizeof(double), cudaMemcpyDeviceToDevice, st));
   if (p->timed) cudaEventRecord(p->ev[4], st);
   return SBX_OK;
+}
+
+extern "C" int sbx_scatter_slab_path(const sbx_slab_plan* p) {
+  if (!p) return SBX_EINVAL;
+  return p->pruned ? SBX_SCATTER_PRUNED_FUSED : SBX_SCATTER_FFT_DENSE;
 }
 
 extern "C" int sbx_scatter_slab_set_profiling(sbx_slab_plan* p, int enable) {
@@ -381,7 +436,23 @@ extern "C" int sbx_scatter_slab_emulate(int device, int world, const int64_t* N,
   int rc = SBX_OK;
   for (int r = 0; r < world && !rc; ++r) rc = slab_build(&plans[r], nullptr, r, world, device, N, L, cutoff, threshold);
   DeviceGuard guard(device);
-  if (!rc) {
+  if (!rc && plans[0]->pruned) {
+    // pruned mode: per-rank mode sums, added on the host in rank order, then one finish
+    const long long slab = (long long)plans[0]->n0 * N[1] * N[2];
+    const int nu = scatter_slab_n_umodes(plans[0]->inner);
+    std::vector<double> acc((size_t)2 * nu, 0.0), part((size_t)2 * nu);
+    for (int r = 0; r < world && !rc; ++r) {
+      rc = scatter_slab_partial(plans[r]->inner, field + (size_t)r * slab, plans[r]->n0, r * plans[r]->n0, plans[r]->d_modesum, st);
+      if (!rc && cudaMemcpyAsync(part.data(), plans[r]->d_modesum, part.size() * sizeof(double), cudaMemcpyDeviceToHost, st) != cudaSuccess)
+        rc = fail(SBX_ECUDA, "mode-sum copy failed");
+      if (!rc && cudaStreamSynchronize(st) != cudaSuccess) rc = fail(SBX_ECUDA, "stream sync failed: %s", cudaGetErrorString(cudaGetLastError()));
+      for (size_t k = 0; k < acc.size() && !rc; ++k) acc[k] += part[k];
+    }
+    if (!rc && cudaMemcpyAsync(plans[0]->d_modesum, acc.data(), acc.size() * sizeof(double), cudaMemcpyHostToDevice, st) != cudaSuccess)
+      rc = fail(SBX_ECUDA, "mode-sum upload failed");
+    if (!rc) rc = scatter_slab_finish(plans[0]->inner, plans[0]->d_modesum, shell_I, st);
+    if (!rc) cudaStreamSynchronize(st);
+  } else if (!rc) {
     const long long slab = (long long)plans[0]->n0 * N[1] * N[2];
     for (int r = 0; r < world && !rc; ++r) rc = slab_stage_a(plans[r], field + (size_t)r * slab, st);
     if (!rc && world > 1)

@@ -147,6 +147,8 @@ class SlabScatter:
         _lib.check(L_.sbx_scatter_slab_shells(self._h, C.byref(n), self.q.ctypes.data_as(C.POINTER(C.c_double)),
                                               self.count.ctypes.data_as(C.POINTER(C.c_int64))))
         self.planes = slab_planes(self.N[0], self.rank, self.world)
+        # 4: pruned DFT (mode sums + one small all-reduce); 1: slab FFT with all-to-all.  SBX_SLAB_PATH=fft|pruned forces one.
+        self.path = int(L_.sbx_scatter_slab_path(self._h))
 
     def execute(self, local_slab, out=None):
         """``local_slab``: CUDA fp64 tensor (N0/world, N1, N2) = this rank's planes.  Returns the
@@ -176,6 +178,8 @@ class SlabScatter:
     def profile(self) -> dict:
         ms = (C.c_double * 4)()
         _lib.check(_lib.lib().sbx_scatter_slab_profile(self._h, ms))
+        if self.path == _lib.PATH_PRUNED_FUSED:
+            return dict(pruned_planes_ms=ms[0], all_reduce_ms=ms[1], finish_ms=ms[3])
         return dict(fft2d_pack_ms=ms[0], all_to_all_ms=ms[1], fft1d_ms=ms[2], histogram_allreduce_ms=ms[3])
 
     def close(self):

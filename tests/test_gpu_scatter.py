@@ -190,6 +190,53 @@ def test_pruned_dft_vs_oracle(sbx_lib, torch_cuda, shape, L, cutoff, path):
         check_scatter_rows(qI, ref, cutoff, last_shell_members(mat, L, cutoff, 1e-12))
 
 
+@pytest.mark.parametrize("shape", [(256, 256, 32), (384, 384, 16), (48, 48, 64), (128, 128, 128), (32, 32, 32)])
+def test_blocked_pruned_kernel_vs_gather(sbx_lib, torch_cuda, monkeypatch, shape):
+    """pruned_blocked_kernel (the form used for 512^3 / 1024^3 planes and for slabs), forced on grids the oracle and
+    the cuFFT gather path can check: 1-3 row blocks, in-kernel finish with peaks, two fields per launch."""
+    from simubox_b200 import Scatter
+
+    monkeypatch.setenv("SBX_FUSED_BLOCKED", "1")
+    rng = np.random.default_rng(sum(shape))
+    mats = [rng.random(shape) for _ in range(2)]
+    L = (6.0, 6.0, 6.0)
+    pk = dict(width=0.5, step=500, cutoff=1e9, min_height=0.0)
+    out = run_scatter(sbx_lib, torch_cuda, mats, L, 30, 1e-12, FUSED, peaks=pk)
+    from simubox_b200.scatter import get_plan
+    assert get_plan(shape, L, 30, 1e-12, max_batch=2, path=FUSED).kernel == "pruned_blocked_kernel"
+    monkeypatch.delenv("SBX_FUSED_BLOCKED")
+    ref = run_scatter(sbx_lib, torch_cuda, mats, L, 30, 1e-12, GATHER, peaks=pk)
+    a, b = out["I"].cpu().numpy(), ref["I"].cpu().numpy()
+    assert np.all(np.abs(a[:, :-1] - b[:, :-1]) <= 1e-9 * np.abs(b[:, :-1]) + 1e-12 * np.abs(b).max())
+    assert np.array_equal(out["n_peaks"].cpu().numpy(), ref["n_peaks"].cpu().numpy())
+    n = int(out["n_peaks"][0])
+    assert np.array_equal(out["peak_idx"][:, :n].cpu().numpy(), ref["peak_idx"][:, :n].cpu().numpy())
+    if shape == (32, 32, 32):
+        want, _ = scatter_np.scattering_peak_table(mats[0], L, 30, 1e-12)
+        check_scatter_rows(np.stack([out["q"], a[0]], axis=1), want, 30, last_shell_members(mats[0], L, 30, 1e-12))
+
+
+def test_giant_grid_uses_the_blocked_kernel(sbx_lib, torch_cuda):
+    """512^3 (1 GB per field): AUTO picks the pruned path with the row-blocked kernel; checked against the cuFFT gather
+    path and through size-independent properties (DC row, x4 under x2 scaling)."""
+    from simubox_b200 import Scatter, synth
+    from simubox_b200.scatter import get_plan
+
+    torch = torch_cuda
+    n, cells = 512, 8
+    L = synth.box_for(cells)
+    f = synth.fields_torch(0, 1, (n, n, n), cells=cells)
+    out = Scatter.sacttering_peak_batch(f, L, max_batch=1)
+    assert out["path"] == "pruned_dft_fused" and get_plan((n, n, n), L, 30, 1e-12, max_batch=1).kernel == "pruned_blocked_kernel"
+    I = out["I"][0].cpu().numpy()
+    ref = Scatter.sacttering_peak_batch(f, L, max_batch=1, path=GATHER)["I"][0].cpu().numpy()
+    assert np.all(np.abs(I[:-1] - ref[:-1]) <= 1e-9 * np.abs(ref[:-1]) + 1e-12 * np.abs(ref).max())
+    total = float(f.sum().item())
+    assert abs(I[0] - total * total / n ** 3) <= 1e-9 * total * total / n ** 3
+    I2 = Scatter.sacttering_peak_batch(2.0 * f, L, max_batch=1)["I"][0].cpu().numpy()
+    assert np.array_equal(I2, 4.0 * I)
+
+
 @pytest.mark.parametrize("width", [0.5, 0.25, 0.3, 1.7, 2.0])
 def test_peak_width_forms_vs_oracle(sbx_lib, torch_cuda, width):
     """Gaussian broadening with power-of-two widths (exact reciprocal multiply on the device) and general widths

@@ -21,9 +21,16 @@ pytestmark = pytest.mark.gpu
     ((8, 12, 10), (1.0, 2.0, 3.0), 10, 2),     # non-cubic, unequal box: quirk Q1 under the row remap
     ((12, 8, 6), (2.0, 1.0, 1.5), 30, 4), ((32, 32, 32), (8.0, 8.0, 8.0), 400, 8),
     ((64, 64, 64), (8.0, 8.0, 8.0), 30, 8)])
-def test_emulated_slab_matches_oracle(sbx_lib, N, L, cutoff, world):
+@pytest.mark.parametrize("slab_path", ["fft", "auto"])
+def test_emulated_slab_matches_oracle(sbx_lib, monkeypatch, N, L, cutoff, world, slab_path):
+    """"fft": the slab FFT + exchange for every case; "auto": the pruned-DFT slab mode wherever it applies
+    (low modes only, N2 % 16 == 0, planes per rank divisible by the unit size), the FFT mode elsewhere."""
     from simubox_b200 import distributed as D
 
+    if slab_path == "fft":
+        monkeypatch.setenv("SBX_SLAB_PATH", "fft")
+    else:
+        monkeypatch.delenv("SBX_SLAB_PATH", raising=False)
     rng = np.random.default_rng(hash((N, world)) % 2 ** 32)
     mat = rng.random(N)
     I = D.slab_emulate(mat, L, world, cutoff=cutoff)
@@ -47,6 +54,24 @@ def test_emulated_slab_equals_single_gpu_plan(sbx_lib):
         assert np.all(np.abs(I[:-1] - one[:-1]) <= tol)
 
 
+@pytest.mark.parametrize("N,world", [((256, 256, 32), 4), ((384, 384, 16), 2), ((48, 48, 64), 4), ((128, 128, 128), 8)])
+def test_pruned_slab_mode_blocked_rows(sbx_lib, monkeypatch, N, world):
+    """Pruned slab mode forced (a plan error if it does not apply): row-blocked planes (N1 = 2 or 3 blocks of 128 rows,
+    or one odd-sized block; N0 = N1, else quirk Q1 scrambles the mode set), x_base offsets of up to 8 ranks, against the cuFFT gather path of the single-GPU plan."""
+    import torch
+
+    from simubox_b200 import Scatter, distributed as D
+
+    monkeypatch.setenv("SBX_SLAB_PATH", "pruned")
+    rng = np.random.default_rng(sum(N))
+    mat = rng.random(N)
+    L = (6.0, 6.0, 6.0)
+    I = D.slab_emulate(mat, L, world)
+    one = Scatter.sacttering_peak_batch(torch.from_numpy(mat[None]).cuda(), L, path=2)["I"][0].cpu().numpy()
+    tol = 1e-9 * np.abs(one[:-1]) + 1e-12 * np.abs(one).max()
+    assert np.all(np.abs(I[:-1] - one[:-1]) <= tol)
+
+
 def test_slab_rejects_bad_partition(sbx_lib):
     from simubox_b200 import distributed as D
 
@@ -55,14 +80,16 @@ def test_slab_rejects_bad_partition(sbx_lib):
     assert ei.value.code == -1
 
 
-def test_nccl_slab_two_ranks():
+@pytest.mark.parametrize("slab_path", ["fft", "pruned"])
+def test_nccl_slab_two_ranks(slab_path):
+    """The real NCCL path, one process per GPU: slab FFT (all-to-all + all-reduce) and pruned mode (all-reduce only)."""
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs (the single-GPU emulation test covers the decomposition)")
     world = 2
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-           "--master-port", "29517", str(ROOT / "tests" / "slab_worker.py"), "--grid", "64"]
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT))
+           "--master-port", "29517" if slab_path == "fft" else "29518", str(ROOT / "tests" / "slab_worker.py"), "--grid", "64"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT), env=dict(os.environ, SBX_SLAB_PATH=slab_path))
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "slab parity ok" in res.stdout
