@@ -237,15 +237,20 @@ __host__ __device__ inline size_t blocked_work_doubles(int yb_rows, int n_shells
   const size_t b = (size_t)n_shells + n_umodes + 2 + (peaks ? (size_t)step + 2 * (size_t)n_shells : 0);
   return a > b ? a : b;
 }
-__host__ __device__ inline size_t blocked_smem_bytes(int N0, size_t work_doubles) {
-  return (2 * (size_t)N0 + work_doubles) * sizeof(double);
+// TWF_SMEM: the z twiddles (N2 / 16 KB) are copied to shared memory when they are at most 32 KB (N2 <= 512) --
+// reading them through L1 costs 10 % at 128^3
+__host__ __device__ inline bool blocked_twf_in_smem(int N2) { return (size_t)(N2 / 16) * 1024 <= 32 * 1024; }
+__host__ __device__ inline size_t blocked_smem_bytes(int N0, int N2, size_t work_doubles) {
+  return (2 * (size_t)N0 + work_doubles + (blocked_twf_in_smem(N2) ? (size_t)(N2 / 16) * 128 : 0)) * sizeof(double);
 }
 
+template <bool TWF_SMEM>
 __global__ void __launch_bounds__(256, 3)
 pruned_blocked_kernel(const FusedArgs A) {
   extern __shared__ double sm[];
   double2* tw0 = reinterpret_cast<double2*>(sm);      // N0
-  double* work = reinterpret_cast<double*>(tw0 + A.N0);
+  double* twf_s = reinterpret_cast<double*>(tw0 + A.N0);  // ds * 128 when TWF_SMEM
+  double* work = twf_s + (TWF_SMEM ? (size_t)A.ds * 128 : 0);
   const int gstride = A.yb_rows + 4;
   double* gT = work;                                  // 16 * gstride
   double* c2 = gT + (size_t)16 * gstride;             // 256
@@ -253,6 +258,8 @@ pruned_blocked_kernel(const FusedArgs A) {
   __shared__ int s_unit, s_last;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < A.N0; i += 256) tw0[i] = A.tw0[i];
+  if (TWF_SMEM)
+    for (int i = tid; i < A.ds * 128; i += 256) twf_s[i] = A.twf[i];
   int4 md[kFusedModesPerThread];
   int orc[kFusedModesPerThread];
 #pragma unroll
@@ -294,11 +301,11 @@ pruned_blocked_kernel(const FusedArgs A) {
 #pragma unroll 4
         for (int s = 0; s < A.ds; ++s) {
           const double2 a = __ldg(row + 4 * s), b = __ldg(row2 + 4 * s);
-          const double* tw = A.twf + s * 128 + lane;
-          dmma_m8n8k4(e0, e1, a.x + b.x, __ldg(tw));
-          dmma_m8n8k4(e0, e1, a.y + b.y, __ldg(tw + 32));
-          dmma_m8n8k4(o0, o1, a.x - b.x, __ldg(tw + 64));
-          dmma_m8n8k4(o0, o1, a.y - b.y, __ldg(tw + 96));
+          const double* tw = (TWF_SMEM ? twf_s : A.twf) + s * 128 + lane;
+          dmma_m8n8k4(e0, e1, a.x + b.x, TWF_SMEM ? tw[0] : __ldg(tw));
+          dmma_m8n8k4(e0, e1, a.y + b.y, TWF_SMEM ? tw[32] : __ldg(tw + 32));
+          dmma_m8n8k4(o0, o1, a.x - b.x, TWF_SMEM ? tw[64] : __ldg(tw + 64));
+          dmma_m8n8k4(o0, o1, a.y - b.y, TWF_SMEM ? tw[96] : __ldg(tw + 96));
         }
         const int y = grp * 8 + m;
         gT[(size_t)re0 * gstride + y] = e0;

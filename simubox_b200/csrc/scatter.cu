@@ -321,7 +321,7 @@ static int build_pruned_tables(sbx_scatter_plan* p) {
     p->yb_rows = N1 % 128 == 0 ? 128 : (N1 <= 256 ? (int)N1 : 0);
     if (p->yb_rows) {
       p->yblocks = (int)(N1 / p->yb_rows);
-      p->blocked_ok = blocked_smem_bytes((int)N0, blocked_work_doubles(p->yb_rows, t.n_shells(), (int)umodes.size(), 2000, true)) <= 200 * 1024;
+      p->blocked_ok = blocked_smem_bytes((int)N0, (int)N2, blocked_work_doubles(p->yb_rows, t.n_shells(), (int)umodes.size(), 2000, true)) <= 200 * 1024;
     }
   }
   if ((rc = upload(&p->d_tw0, tw0))) return rc;
@@ -478,7 +478,8 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   cudaFuncSetAttribute(pruned_planes_fullk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_fused_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
-  cudaFuncSetAttribute(pruned_blocked_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(pruned_blocked_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
+  cudaFuncSetAttribute(pruned_blocked_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(fused_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_ring_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
   cudaFuncSetAttribute(pruned_ring_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
@@ -580,7 +581,7 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
       A.chunks = g.N0 / A.xc; A.parts = A.chunks * A.yblocks;
       const size_t bwork = blocked_work_doubles(p->yb_rows, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks);
       A.work_doubles = (int)bwork;
-      const size_t bsmem = blocked_smem_bytes(g.N0, bwork);
+      const size_t bsmem = blocked_smem_bytes(g.N0, g.N2, bwork);
       if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
       p->last_kernel = "pruned_blocked_kernel";
       for (int c0 = 0; c0 < batch; c0 += p->chunk) {
@@ -595,7 +596,8 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
         const long long units = (long long)nb * A.parts;
         const int grid = (int)std::min<long long>(units, (long long)p->pruned_ctas_per_sm * p->sm_count);
         if (p->profiling) prof_event(p, st);
-        pruned_blocked_kernel<<<grid, 256, bsmem, st>>>(A);
+        if (blocked_twf_in_smem(g.N2)) pruned_blocked_kernel<true><<<grid, 256, bsmem, st>>>(A);
+        else pruned_blocked_kernel<false><<<grid, 256, bsmem, st>>>(A);
         SBX_CUDA(cudaGetLastError());
         if (p->profiling) { prof_event(p, st); prof_event(p, st); }
         p->own_launches += 1;
@@ -814,11 +816,12 @@ int scatter_slab_partial(sbx_scatter_plan* p, const double* slab, int planes, in
   A.chunks = planes / A.xc; A.parts = A.chunks * A.yblocks;
   const size_t bwork = blocked_work_doubles(p->yb_rows, A.n_shells, p->n_umodes, 0, false);
   A.work_doubles = (int)bwork;
-  const size_t bsmem = blocked_smem_bytes(A.N0, bwork);
+  const size_t bsmem = blocked_smem_bytes(A.N0, A.N2, bwork);
   if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
   SBX_CUDA(cudaMemsetAsync(p->d_ctrl, 0, 2 * sizeof(unsigned), st));
   const int grid = (int)std::min<long long>(A.parts, (long long)p->pruned_ctas_per_sm * p->sm_count);
-  pruned_blocked_kernel<<<grid, 256, bsmem, st>>>(A);
+  if (blocked_twf_in_smem(A.N2)) pruned_blocked_kernel<true><<<grid, 256, bsmem, st>>>(A);
+  else pruned_blocked_kernel<false><<<grid, 256, bsmem, st>>>(A);
   SBX_CUDA(cudaGetLastError());
   fused_reduce_parts_kernel<<<(p->n_umodes + 127) / 128, 128, 0, st>>>(p->d_partial, A.parts, p->n_umodes, modesum);
   SBX_CUDA(cudaGetLastError());
