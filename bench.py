@@ -586,7 +586,7 @@ def main():
     ap.add_argument("--grid", type=int, default=128)
     ap.add_argument("--cells", type=int, default=2)
     ap.add_argument("--fields", type=int, default=256)
-    ap.add_argument("--max-batch", type=int, default=128, help="fields per kernel launch (device-resident path)")
+    ap.add_argument("--max-batch", type=int, default=256, help="fields per kernel launch (device-resident path)")
     ap.add_argument("--host-batch", type=int, default=16, help="fields per H2D chunk of the host-streaming path")
     ap.add_argument("--e2e-steps", type=int, default=3)
     ap.add_argument("--cpu-fields", type=int, default=0)

@@ -360,14 +360,27 @@ extern "C" int sbx_domain_centres(int device, int ndim, const int64_t* N, const 
   DeviceGuard guard(device);
   cudaStream_t st = static_cast<cudaStream_t>(stream);
   const int n_chunks = (int)((g.n + kChunk - 1) / kChunk);
+  // stream-ordered scratch, returned to the pool on every exit path
+  struct Scratch {
+    cudaStream_t st;
+    void* ptrs[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    int n = 0;
+    explicit Scratch(cudaStream_t s) : st(s) {}
+    ~Scratch() { for (int i = 0; i < n; ++i) cudaFreeAsync(ptrs[i], st); }
+    cudaError_t get(void** p, size_t bytes) {
+      const cudaError_t e = cudaMallocAsync(p, bytes, st);
+      if (e == cudaSuccess) ptrs[n++] = *p;
+      return e;
+    }
+  } scratch(st);
   int *parent = nullptr, *chunk = nullptr, *roots = nullptr, *own_comp = nullptr;
   long long* acc = nullptr;
-  SBX_CUDA(cudaMallocAsync(&parent, (size_t)g.n * sizeof(int), st));
-  SBX_CUDA(cudaMallocAsync(&chunk, ((size_t)n_chunks + 1) * sizeof(int), st));
-  SBX_CUDA(cudaMallocAsync(&roots, (size_t)max_components * sizeof(int), st));
-  SBX_CUDA(cudaMallocAsync(&acc, (size_t)max_components * 4 * sizeof(long long), st));
+  SBX_CUDA(scratch.get((void**)&parent, (size_t)g.n * sizeof(int)));
+  SBX_CUDA(scratch.get((void**)&chunk, ((size_t)n_chunks + 1) * sizeof(int)));
+  SBX_CUDA(scratch.get((void**)&roots, (size_t)max_components * sizeof(int)));
+  SBX_CUDA(scratch.get((void**)&acc, (size_t)max_components * 4 * sizeof(long long)));
   if (!comp_labels) {
-    SBX_CUDA(cudaMallocAsync(&own_comp, (size_t)g.n * sizeof(int), st));
+    SBX_CUDA(scratch.get((void**)&own_comp, (size_t)g.n * sizeof(int)));
     comp_labels = own_comp;
   }
   SBX_CUDA(cudaMemsetAsync(acc, 0, (size_t)max_components * 4 * sizeof(long long), st));
@@ -395,10 +408,5 @@ extern "C" int sbx_domain_centres(int device, int ndim, const int64_t* N, const 
     seeds_finalize_kernel<<<(unsigned)((filled + 127) / 128), 128, 0, st>>>(g, ndim, roots, acc, filled, centres, reinterpret_cast<long long*>(volumes));
     SBX_CUDA(cudaGetLastError());
   }
-  cudaFreeAsync(parent, st);
-  cudaFreeAsync(chunk, st);
-  cudaFreeAsync(roots, st);
-  cudaFreeAsync(acc, st);
-  if (own_comp) cudaFreeAsync(own_comp, st);
   return SBX_OK;
 }

@@ -133,8 +133,9 @@ def test_host_streaming_entry_point(sbx_lib, torch_cuda):
         out = Scatter.sacttering_peak_batch(src, L, peaks=True, max_batch=3, path=GATHER)
         assert np.array_equal(out["I"], dev["I"].cpu().numpy())
         assert np.array_equal(out["n_peaks"], dev["n_peaks"].cpu().numpy())
-        n = int(out["n_peaks"][0])
-        assert np.array_equal(out["peak_idx"][:, :n], dev["peak_idx"][:, :n].cpu().numpy())
+        for b in range(len(mats)):
+            n = int(out["n_peaks"][b])
+            assert np.array_equal(out["peak_idx"][b, :n], dev["peak_idx"][b, :n].cpu().numpy())
 
 
 @pytest.mark.parametrize("n,cells", [(128, 2), (256, 4)])
@@ -209,8 +210,9 @@ def test_blocked_pruned_kernel_vs_gather(sbx_lib, torch_cuda, monkeypatch, shape
     a, b = out["I"].cpu().numpy(), ref["I"].cpu().numpy()
     assert np.all(np.abs(a[:, :-1] - b[:, :-1]) <= 1e-9 * np.abs(b[:, :-1]) + 1e-12 * np.abs(b).max())
     assert np.array_equal(out["n_peaks"].cpu().numpy(), ref["n_peaks"].cpu().numpy())
-    n = int(out["n_peaks"][0])
-    assert np.array_equal(out["peak_idx"][:, :n].cpu().numpy(), ref["peak_idx"][:, :n].cpu().numpy())
+    for b in range(2):  # entries beyond a field's own count are unspecified
+        n = int(out["n_peaks"][b])
+        assert np.array_equal(out["peak_idx"][b, :n].cpu().numpy(), ref["peak_idx"][b, :n].cpu().numpy())
     if shape == (32, 32, 32):
         want, _ = scatter_np.scattering_peak_table(mats[0], L, 30, 1e-12)
         check_scatter_rows(np.stack([out["q"], a[0]], axis=1), want, 30, last_shell_members(mats[0], L, 30, 1e-12))
