@@ -30,6 +30,14 @@ if str(ROOT) not in sys.path:
 PEAK_KW = dict(width=0.5, step=2000, cutoff=20, min_height=1)
 
 
+def measured_traffic(key):
+    """DRAM bytes per launch of the dominant kernel from the committed ncu --set full capture, or None."""
+    try:
+        return json.loads((ROOT / "profiles" / "traffic.json").read_text()).get(key, {}).get("bytes")
+    except Exception:
+        return None
+
+
 def measured_peak_gbs():
     p = ROOT / "MEASURED_PEAKS.json"
     if p.exists():
@@ -292,7 +300,8 @@ def run_scatter(args):
     fields_per_launch = B / max(launches_per_step, 1)
     achieved = unit_bytes * fields_per_launch / (fused_ms_per_launch * 1e-3) / 1e9 if fused_ms_per_launch > 0 else None
     roof = {"bound": "hbm", "kernel": kern, "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": (achieved / peak) if achieved else None, "traffic": None, "peak_source": peak_src,
+            "frac": (achieved / peak) if achieved else None,
+            "traffic": measured_traffic(f"{kern}|{n}^3|{int(round(fields_per_launch))} fields/launch"), "peak_source": peak_src,
             "algorithmic_bytes_per_field": unit_bytes, "fields_per_launch": fields_per_launch,
             "kernel_ms_per_launch": fused_ms_per_launch,
             "step_split_ms": ({kern: transform_ms_per_step} if plan.path == 4 else
@@ -421,7 +430,8 @@ def run_voronoi(args):
                 "d2h_bytes_per_step": grids * vox * 4, "ms_per_step": e2e_ms, "api": "VoronoiCell.label_grid(host seeds, host mask) -> host labels"},
         "gpu_launches": 3 * grids * args.steps,
         "roofline": {"bound": "hbm", "kernel": "coarse_kernel+mid_kernel+label_kernel", "achieved": achieved, "peak": peak,
-                     "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                     "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(f"coarse_kernel+mid_kernel+label_kernel|{n}^3|{S} seeds"),
+                     "peak_source": peak_src,
                      "algorithmic_bytes_per_grid": unit_bytes, "evaluations_per_live_voxel": st["evaluations"] / max(live, 1),
                      "overflow_tiles": st["overflow_tiles"]},
         "cpu_baseline": {"value": cpu_rate, "unit": "voxels/s", "cores": cores, "kind": "port",

@@ -2,8 +2,8 @@
 # One gpurun call: smoke, GPU parity suite, both bench workloads + reference arm, ncu launch lists and one
 # full capture per top kernel (each only after the identical command exited 0 without ncu).
 set -u
-mkdir -p gpurun_out/final
-O=gpurun_out/final
+mkdir -p gpurun_out/final5
+O=gpurun_out/final5
 python -c "import __graft_entry__ as g; g.smoke()" > $O/smoke.log 2>&1; echo "smoke rc=$?"; tail -2 $O/smoke.log
 timeout 1500 python -m pytest tests -m gpu -x -q > $O/pytest_gpu.log 2>&1; echo "pytest rc=$?"; tail -3 $O/pytest_gpu.log
 python bench.py > $O/bench_scatter.json 2> $O/bench_scatter.err; echo "bench scatter rc=$?"; cat $O/bench_scatter.json
