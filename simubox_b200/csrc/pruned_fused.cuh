@@ -621,4 +621,179 @@ pruned_ring_kernel(const FusedArgs A) {
   }
 }
 
+// ------------------------------------------------------------------------------------------
+// Bulk-staged blocked variant (giant grids: 512^3, 1024^3, and the slabs of one field spread over GPUs).
+// The LDG blocked kernel reads a row group as 16 streams of 64-byte pieces (8 rows x 2 halves, rows 4-8 KB
+// apart): at N2 = 1024 that reaches ~52 % of the HBM peak.  Here every warp owns a private two-stage pipeline
+// in shared memory.  One pipeline item = one segment of 64 samples of both halves of the warp's 8 rows:
+// 16 pieces of 512 contiguous bytes, each fetched by one TMA bulk copy (cp.async.bulk + mbarrier complete_tx;
+// SASS UBLKCP) issued by lanes 0..15.  The warp transforms the stage that has landed while the other one is
+// in flight; the item sequence of a warp runs through all segments, row groups and planes of its unit, so
+// copies stay in flight across the plane barriers and the y / x stages.  Accumulators live in registers across
+// the segments of a row group.  Stage layout: pieces of even rows | 64 B | pieces of odd rows, so that the two
+// rows a quarter-warp reads with one 16-byte load per lane fall into disjoint banks.
+// One CTA of 8 warps per SM: 2 x 8 x 8.06 KB of stages + the z twiddles (N2 x 64 B) + the unit's work area.
+// Requires N2 % 128 == 0 and yb_rows % 64 == 0.  Same unit / partial-sum / finish scheme, hence the same bits,
+// as pruned_blocked_kernel.
+// ------------------------------------------------------------------------------------------
+constexpr int kBulkSeg = 64;                                  // doubles per piece
+constexpr int kBulkPiece = kBulkSeg * 8;                      // 512 bytes
+constexpr int kBulkStageBytes = 16 * kBulkPiece + 64;
+constexpr int kBulkStages = 2;
+__host__ __device__ inline size_t bulk_smem_bytes(int N2, size_t work_doubles) {
+  return (size_t)8 * kBulkStages * kBulkStageBytes + (size_t)8 * kBulkStages * 8 + ((size_t)(N2 / 16) * 128 + work_doubles) * sizeof(double);
+}
+__device__ __forceinline__ int bulk_piece_offset(int row, int half) {
+  return ((row >> 1) * 2 + half) * kBulkPiece + (row & 1) * (8 * kBulkPiece + 64);
+}
+
+__global__ void __launch_bounds__(256, 1)
+pruned_bulk_kernel(const FusedArgs A) {
+  extern __shared__ __align__(128) unsigned char smraw[];
+  unsigned char* stages = smraw;                                            // [8 warps][kBulkStages][kBulkStageBytes]
+  uint64_t* bars = reinterpret_cast<uint64_t*>(stages + (size_t)8 * kBulkStages * kBulkStageBytes);
+  double* twf = reinterpret_cast<double*>(bars + 8 * kBulkStages);         // ds * 128
+  double* work = twf + (size_t)A.ds * 128;
+  const int gstride = A.yb_rows + 4;
+  double* gT = work;                                  // 16 * gstride
+  double* c2 = gT + (size_t)16 * gstride;             // 256
+  double* hp = c2 + 256;                              // 256
+  __shared__ int s_unit, s_last;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  for (int i = tid; i < A.ds * 128; i += 256) twf[i] = A.twf[i];
+  if (tid < 8 * kBulkStages) pf_mbar_init(&bars[tid], 1);
+  asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  int4 md[kFusedModesPerThread];
+  int orc[kFusedModesPerThread];
+#pragma unroll
+  for (int k = 0; k < kFusedModesPerThread; ++k) {
+    const int u = tid + 256 * k;
+    md[k] = u < A.n_umodes ? A.umodes[u] : make_int4(0, 0, 0, 0);
+    orc[k] = md[k].z * 16 + (md[k].y < 0 ? -md[k].y : md[k].y);
+  }
+  const int m = lane >> 2, kk = lane & 3;
+  const int gpw = A.yb_rows >> 6;          // row groups per warp and plane (groups / 8)
+  const int nseg = A.N2 >> 7;              // segments per row: (N2 / 2) / kBulkSeg
+  const int ksb = A.yb_rows >> 2;
+  const int n_units = A.n_fields * A.parts;
+  const int n_items = A.xc * gpw * nseg;   // pipeline items of one warp in one unit
+  const long long plane_doubles = (long long)A.N1 * A.N2;
+  const int n0 = 2 * kk, n1 = 2 * kk + 1;
+  const int re0 = n0 < 4 ? 2 * n0 : 8 + 2 * (n0 - 4), re1 = n1 < 4 ? 2 * n1 : 8 + 2 * (n1 - 4);
+  unsigned char* my_stages = stages + (size_t)warp * kBulkStages * kBulkStageBytes;
+  uint64_t* my_bars = bars + warp * kBulkStages;
+  // this lane's two pieces of a stage (A fragment: row m, samples 2 kk, 2 kk + 1 of every 8)
+  const int off_a = bulk_piece_offset(m, 0) + kk * 16;
+  // lanes 0..15 fetch piece (row = lane & 7, half = lane >> 3)
+  const int put_off = bulk_piece_offset(lane & 7, (lane >> 3) & 1);
+  const long long put_src = (long long)(lane & 7) * A.N2 + (long long)((lane >> 3) & 1) * (A.N2 >> 1);
+  unsigned it = 0;  // items this warp has consumed so far (all units): stage = it % 2, parity = (it / 2) % 2
+  __syncthreads();
+
+  for (;;) {
+    if (tid == 0) s_unit = (int)atomicAdd(&A.ctrl[0], 1u);
+    __syncthreads();
+    const int unit = s_unit;
+    if (unit >= n_units) break;
+    const int field = unit / A.parts, part = unit - field * A.parts;
+    const int chunk = part / A.yblocks, yb = part - chunk * A.yblocks;
+    const int x0 = chunk * A.xc;
+    const double* ubase = A.fields + ((long long)field * A.planes + x0) * plane_doubles + (long long)yb * A.yb_rows * A.N2;
+    // request item i of this unit into stage st (whole warp)
+    auto issue = [&](int i, int st) {
+      const int sg = i % nseg, t2 = i / nseg;
+      const int gi = t2 % gpw, xi = t2 / gpw;
+      const double* src = ubase + (long long)xi * plane_doubles + (long long)((warp + 8 * gi) * 8) * A.N2 + sg * kBulkSeg;
+      if (lane == 0) pf_mbar_expect_tx(&my_bars[st], 16 * kBulkPiece);
+      __syncwarp();
+      if (lane < 16) pf_bulk_g2s(my_stages + (size_t)st * kBulkStageBytes + put_off, src + put_src, kBulkPiece, &my_bars[st]);
+    };
+    issue(0, it & 1u);
+    if (n_items > 1) issue(1, (it + 1u) & 1u);
+    double fr[kFusedModesPerThread], fi[kFusedModesPerThread];
+    int jj[kFusedModesPerThread];
+#pragma unroll
+    for (int k = 0; k < kFusedModesPerThread; ++k) {
+      fr[k] = 0.0; fi[k] = 0.0;
+      jj[k] = (int)(((long long)md[k].x * (A.x_base + x0)) % A.N0);
+    }
+    int item = 0;
+    for (int xi = 0; xi < A.xc; ++xi) {
+      // ---- stage 1 (z, folded): this warp's row groups, segment by segment out of its pipeline
+      for (int gi = 0; gi < gpw; ++gi) {
+        double e0 = 0.0, e1 = 0.0, o0 = 0.0, o1 = 0.0;
+        for (int sg = 0; sg < nseg; ++sg, ++item, ++it) {
+          const int st = it & 1u;
+          pf_mbar_wait(&my_bars[st], (it >> 1) & 1u);
+          const double2* ra = reinterpret_cast<const double2*>(my_stages + (size_t)st * kBulkStageBytes + off_a);
+          const double2* rb = ra + kBulkPiece / 16;
+          const double* tws = twf + (size_t)sg * (kBulkSeg / 8) * 128 + lane;
+#pragma unroll
+          for (int s = 0; s < kBulkSeg / 8; ++s) {
+            const double2 a = ra[4 * s], b = rb[4 * s];
+            const double* tw = tws + s * 128;
+            dmma_m8n8k4(e0, e1, a.x + b.x, tw[0]);
+            dmma_m8n8k4(e0, e1, a.y + b.y, tw[32]);
+            dmma_m8n8k4(o0, o1, a.x - b.x, tw[64]);
+            dmma_m8n8k4(o0, o1, a.y - b.y, tw[96]);
+          }
+          __syncwarp();
+          asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+          if (item + 2 < n_items) issue(item + 2, st);
+        }
+        const int y = (warp + 8 * gi) * 8 + m;
+        gT[(size_t)re0 * gstride + y] = e0;
+        gT[(size_t)re1 * gstride + y] = e1;
+        gT[(size_t)(re0 + 1) * gstride + y] = o0;
+        gT[(size_t)(re1 + 1) * gstride + y] = o1;
+      }
+      __syncthreads();
+      // ---- stage 2 (y): 16 x 16 x yb_rows product with this block's slice of the twiddles
+      {
+        const int mt = warp & 1, nt = (warp >> 1) & 1, kh = warp >> 2;
+        const int s0 = kh * (ksb >> 1), s1 = s0 + (ksb >> 1);
+        const double* arow = gT + (size_t)(8 * mt + m) * gstride;
+        const double* brow = A.tw1 + ((size_t)nt * A.ks1 + (size_t)yb * ksb) * 32;
+        double d0 = 0.0, d1 = 0.0;
+#pragma unroll 4
+        for (int s = s0; s < s1; ++s) dmma_m8n8k4(d0, d1, arow[4 * s + kk], __ldg(brow + s * 32 + lane));
+        const int r = 8 * mt + m, c = 8 * nt + 2 * kk;
+        if (kh == 1) { c2[r * 16 + c] = d0; c2[r * 16 + c + 1] = d1; }
+        __syncthreads();
+        if (kh == 0) { hp[r * 16 + c] = d0 + c2[r * 16 + c]; hp[r * 16 + c + 1] = d1 + c2[r * 16 + c + 1]; }
+      }
+      __syncthreads();
+      // ---- stage 3 (x)
+#pragma unroll
+      for (int k = 0; k < kFusedModesPerThread; ++k) {
+        if (tid + 256 * k < A.n_umodes) {
+          const double rc = hp[orc[k]], rs = hp[orc[k] + 8], sc = hp[orc[k] + 128], ss = hp[orc[k] + 136];
+          const double hr = md[k].y >= 0 ? rc - ss : rc + ss;
+          const double hi = md[k].y >= 0 ? -(rs + sc) : rs - sc;
+          const double2 w = __ldg(A.tw0 + jj[k]);
+          fr[k] += hr * w.x + hi * w.y;
+          fi[k] += hi * w.x - hr * w.y;
+          jj[k] += md[k].x;
+          if (jj[k] >= A.N0) jj[k] -= A.N0;
+        }
+      }
+    }
+    double2* part_out = A.partial + (long long)unit * A.n_umodes;
+#pragma unroll
+    for (int k = 0; k < kFusedModesPerThread; ++k)
+      if (tid + 256 * k < A.n_umodes) part_out[tid + 256 * k] = make_double2(fr[k], fi[k]);
+    if (A.finish) {
+      __threadfence();
+      __syncthreads();
+      if (tid == 0) s_last = atomicAdd(&A.ctrl[1 + field], 1u) == (unsigned)(A.parts - 1);
+      __syncthreads();
+      if (s_last) {
+        __threadfence();
+        fused_finish(A, field, work);
+      }
+    }
+    __syncthreads();
+  }
+}
+
 }  // namespace sbx

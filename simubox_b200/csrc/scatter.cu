@@ -483,6 +483,7 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   cudaFuncSetAttribute(fused_finish_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(pruned_ring_kernel<16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
   cudaFuncSetAttribute(pruned_ring_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
+  cudaFuncSetAttribute(pruned_bulk_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxTmaSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
   cudaFuncSetAttribute(shell_histogram_kernel<3>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kMaxDynSmem);
@@ -546,6 +547,16 @@ static int check_peaks_args(int n, int step, int max_peaks) {
 
 namespace sbx { static int blocked_unit_planes(const sbx_scatter_plan* p, int n_fields, int planes); }
 
+// The bulk-staged form of the blocked kernel (pruned_bulk_kernel) applies when rows split into 512-byte pieces per
+// half (N2 % 128 == 0), a block of rows gives every warp whole row groups (yb_rows % 64 == 0) and the stages, the z
+// twiddles and the work area fit one CTA's shared memory.  Measured on B200 (profiles/r01): see DESIGN.md section 3.
+// SBX_BULK=0 keeps the LDG blocked kernel (read per call: the tests switch it).
+static bool bulk_applies(const sbx_scatter_plan* p, size_t bwork) {
+  const char* e = getenv("SBX_BULK");
+  if (e && atoi(e) == 0) return false;
+  return p->grid.N2 % 128 == 0 && p->yb_rows % 64 == 0 && bulk_smem_bytes(p->grid.N2, bwork) <= kMaxTmaSmem;
+}
+
 // scatter (+ optional fused peaks) on `batch` device-resident fields
 static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, double* shell_I, bool do_peaks,
                        const PeakParams& pp, double* plot_y, int32_t* peak_idx, int32_t* n_peaks,
@@ -583,7 +594,8 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
       A.work_doubles = (int)bwork;
       const size_t bsmem = blocked_smem_bytes(g.N0, g.N2, bwork);
       if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
-      p->last_kernel = "pruned_blocked_kernel";
+      const bool bulk = bulk_applies(p, bwork);
+      p->last_kernel = bulk ? "pruned_bulk_kernel" : "pruned_blocked_kernel";
       for (int c0 = 0; c0 < batch; c0 += p->chunk) {
         const int nb = std::min(p->chunk, batch - c0);
         A.fields = fields + (size_t)c0 * g.nreal;
@@ -596,7 +608,8 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
         const long long units = (long long)nb * A.parts;
         const int grid = (int)std::min<long long>(units, (long long)p->pruned_ctas_per_sm * p->sm_count);
         if (p->profiling) prof_event(p, st);
-        if (blocked_twf_in_smem(g.N2)) pruned_blocked_kernel<true><<<grid, 256, bsmem, st>>>(A);
+        if (bulk) pruned_bulk_kernel<<<(int)std::min<long long>(units, p->sm_count), 256, bulk_smem_bytes(g.N2, bwork), st>>>(A);
+        else if (blocked_twf_in_smem(g.N2)) pruned_blocked_kernel<true><<<grid, 256, bsmem, st>>>(A);
         else pruned_blocked_kernel<false><<<grid, 256, bsmem, st>>>(A);
         SBX_CUDA(cudaGetLastError());
         if (p->profiling) { prof_event(p, st); prof_event(p, st); }
@@ -820,13 +833,15 @@ int scatter_slab_partial(sbx_scatter_plan* p, const double* slab, int planes, in
   if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
   SBX_CUDA(cudaMemsetAsync(p->d_ctrl, 0, 2 * sizeof(unsigned), st));
   const int grid = (int)std::min<long long>(A.parts, (long long)p->pruned_ctas_per_sm * p->sm_count);
-  if (blocked_twf_in_smem(A.N2)) pruned_blocked_kernel<true><<<grid, 256, bsmem, st>>>(A);
+  const bool bulk = bulk_applies(p, bwork);
+  if (bulk) pruned_bulk_kernel<<<(int)std::min<long long>(A.parts, p->sm_count), 256, bulk_smem_bytes(A.N2, bwork), st>>>(A);
+  else if (blocked_twf_in_smem(A.N2)) pruned_blocked_kernel<true><<<grid, 256, bsmem, st>>>(A);
   else pruned_blocked_kernel<false><<<grid, 256, bsmem, st>>>(A);
   SBX_CUDA(cudaGetLastError());
   fused_reduce_parts_kernel<<<(p->n_umodes + 127) / 128, 128, 0, st>>>(p->d_partial, A.parts, p->n_umodes, modesum);
   SBX_CUDA(cudaGetLastError());
   p->own_launches += 2;
-  p->last_kernel = "pruned_blocked_kernel";
+  p->last_kernel = bulk ? "pruned_bulk_kernel" : "pruned_blocked_kernel";
   return SBX_OK;
 }
 

@@ -156,6 +156,13 @@ __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
       : "memory");
 }
 
+// Programmatic dependent launch (PDL): the three kernels of one labelling are chained with
+// cudaLaunchAttributeProgrammaticStreamSerialization, so a kernel's CTAs are scheduled (and run their
+// prologue) while the previous kernel drains; pdl_wait() returns once the previous grid has completed and its
+// writes are visible.  Both are no-ops in a kernel launched without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_trigger() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
+
 __device__ __forceinline__ double warp_min(double v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v = fmin(v, __shfl_xor_sync(kFull, v, o));
@@ -226,6 +233,7 @@ coarse_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restri
               int* __restrict__ clist, int* __restrict__ ccount) {
   constexpr int kRounds = 16, kChunk = 256 * kRounds;
   const int tile = blockIdx.x, tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  pdl_trigger();
   int t[3];
   tile_coords(g.nc, tile, t);
   double c[3], h[3];
@@ -318,6 +326,7 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
   __shared__ int s_ki[4][kCap];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
   const int tile = blockIdx.x * 4 + warp;
+  pdl_trigger();
   if (tile >= n_mid) return;
   int t[3];
   tile_coords(g.nm, tile, t);
@@ -331,6 +340,7 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
     h[a] = 0.5 * (hi - lo);
     parent = parent * g.nc[a] + (t[a] * g.M[a]) / g.C[a];
   }
+  pdl_wait();  // the coarse lists
   const int pc = ccount[parent];
   const int* src = pc <= kCoarseCap ? clist + (long long)parent * kCoarseCap : nullptr;
   const long long n = src ? pc : g.S;
@@ -413,8 +423,39 @@ __device__ __forceinline__ double seed_value(const VorGeo& g, const double* __re
   return __dsub_rn(g.mode == 1 ? __dmul_rn(r, r) : r, w);
 }
 
-// rare path of the unweighted compare, kept out of line so that the inner loop stays small
-__device__ __noinline__ bool sqrt_less(double a, double b) { return __dsqrt_rn(a) < __dsqrt_rn(b); }
+// Rare path of the unweighted compare, kept out of line so that the inner loop stays small: one column of kCol
+// voxels against the warp's surviving records, in the reference's order.  Sums of squares are compared; when a
+// strictly smaller sum is within 8 ulps of the running minimum the rounded roots decide, as in the reference
+// (equal roots leave the voxel with the earlier, lower index: np.argmin).
+struct Col8 { int v[kCol]; };
+template <int ND>
+__device__ __noinline__ Col8 column_exact(const SeedRec* rec, const int* idx, const unsigned char* list, int kept, double X,
+                                          double Y, int z0) {
+  Col8 out;
+  double bs[kCol];
+#pragma unroll
+  for (int k = 0; k < kCol; ++k) { bs[k] = INFINITY; out.v[k] = -1; }
+  for (int j = 0; j < kept; ++j) {
+    const int c = list[j];
+    const SeedRec R = rec[c];
+    const int id = idx[c];
+    const double dy = __dsub_rn(R.y, Y);
+    double sxy = __dmul_rn(dy, dy);
+    if (ND == 3) {
+      const double dx = __dsub_rn(R.x, X);
+      sxy = __dadd_rn(__dmul_rn(dx, dx), sxy);
+    }
+#pragma unroll
+    for (int k = 0; k < kCol; ++k) {
+      const double dz = __dsub_rn(R.z, (double)(z0 + k));
+      const double ss = __dadd_rn(sxy, __dmul_rn(dz, dz));
+      bool take = ss < bs[k];
+      if (take && __double_as_longlong(bs[k]) - __double_as_longlong(ss) <= 8) take = __dsqrt_rn(ss) < __dsqrt_rn(bs[k]);
+      if (take) { bs[k] = ss; out.v[k] = id; }
+    }
+  }
+  return out;
+}
 
 // Warp / lane geometry of the label kernel.  A CTA of 8 warps labels HALF a mid tile (split along the
 // last axis).  3D: mid tile 16^3, half = 16 x 16 x 8 = 4 x 2 warps of 4 x 8 x 8 voxels;
@@ -461,6 +502,7 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   int lx, ly;
   WT::lane_xy(lane, lx, ly);
+  pdl_wait();  // the staged records of the mid kernel
   const int raw = rcount[tile];
   const int count = raw & (kFlagGeneric - 1);
   const bool generic = MODE == 0 || (raw & kFlagGeneric) != 0;
@@ -595,6 +637,7 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
       // ---- evaluation: column of kCol voxels per thread; (z_c - z_k)^2 shared by the warp, 4 candidates a batch
       const double X = (double)vx, Y = (double)vy;
       double bs[kCol];
+      unsigned gap = 0xffffffffu;
 #pragma unroll
       for (int k = 0; k < kCol; ++k) bs[k] = INFINITY;
       for (int b0 = 0; b0 < kept; b0 += 4) {
@@ -628,9 +671,14 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
               const int k = 2 * k2 + q;
               const double ss = __dadd_rn(sxy, q ? d2.y : d2.x);
               if (MODE == 1) {
-                bool take = ss < bs[k];
-                // sums within 8 ulps: their roots may round together, then the earlier index stays (rare branch)
-                if (take && __double_as_longlong(bs[k]) - __double_as_longlong(ss) <= 8) take = sqrt_less(ss, bs[k]);
+                // branch-free: the 8 voxels of the column are independent chains.  A strictly smaller sum within
+                // 8 ulps of the running minimum is the only case where the reference's rounded roots could tie and
+                // leave the voxel with the lower index.  Here only the smallest gap between the high words of a
+                // replaced minimum and its replacement is kept (<= 1 for anything within 2^-20 relative, a superset
+                // of the 8-ulp case); such a column is redone exactly below.
+                const bool take = ss < bs[k];
+                const unsigned dh = (unsigned)__double2hiint(bs[k]) - (unsigned)__double2hiint(ss);
+                gap = take ? min(gap, dh) : gap;
                 bs[k] = take ? ss : bs[k];
                 bi[k] = take ? idx : bi[k];
               } else {
@@ -641,6 +689,11 @@ label_kernel(VorGeo g, const double* __restrict__ seeds, const double* __restric
           }
         }
         __syncwarp();
+      }
+      if (MODE == 1 && gap <= 1u) {  // rare (near ties): this thread's column again, roots compared where needed
+        const Col8 ex = column_exact<ND>(s_rec, s_idx, s_list[warp], kept, X, Y, z0);
+#pragma unroll
+        for (int k = 0; k < kCol; ++k) bi[k] = ex.v[k];
       }
       evals += (unsigned long long)kept * (unsigned long long)__popc(live);
     }
@@ -678,7 +731,24 @@ static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, c
                            int* clist, int* ccount, SeedRec* rec, int* ridx, int* rcount, const uint8_t* mask,
                            int32_t* labels, unsigned long long* stats, cudaStream_t st) {
   coarse_kernel<ND><<<(unsigned)ctiles, 256, 0, st>>>(g, seeds, weights, clist, ccount);
-  mid_kernel<ND><<<(unsigned)((tiles + 3) / 4), 128, 0, st>>>(g, (int)tiles, seeds, weights, clist, ccount, rec, ridx, rcount);
+  static const int pdl = [] { const char* e = getenv("SBX_VOR_PDL"); return e ? atoi(e) : 1; }();
+  cudaLaunchAttribute pdl_attr[1];
+  pdl_attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  pdl_attr[0].val.programmaticStreamSerializationAllowed = 1;
+  auto config = [&](dim3 grid, unsigned threads) {
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = grid;
+    cfg.blockDim = dim3(threads);
+    cfg.dynamicSmemBytes = 0;
+    cfg.stream = st;
+    cfg.attrs = pdl_attr;
+    cfg.numAttrs = pdl ? 1 : 0;
+    return cfg;
+  };
+  {
+    const cudaLaunchConfig_t cfg = config(dim3((unsigned)((tiles + 3) / 4)), 128);
+    cudaLaunchKernelEx(&cfg, mid_kernel<ND>, g, (int)tiles, seeds, weights, (const int*)clist, (const int*)ccount, rec, ridx, rcount);
+  }
   // (warps per CTA, warp tiles per warp).  Measured at 256^3 / 4096 seeds: (8,1) 0.124 ms, (4,1) 0.110 ms, (4,2) 0.118,
   // (4,4) 0.121, (2,8) 0.126: small CTAs recycle their SM slot sooner; more rounds per warp cost registers.
   static const int lw = [] { const char* e = getenv("SBX_LABEL_WARPS"); const int v = e ? atoi(e) : 4; return v == 2 || v == 8 ? v : 4; }();
@@ -688,7 +758,9 @@ static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, c
     auto go = [&](auto w_tag, auto r_tag) {
       constexpr int W = decltype(w_tag)::value, R = decltype(r_tag)::value;
       const dim3 lgrid((unsigned)((16 / (W * R)) * g.nm[2]), (unsigned)g.nm[1], (unsigned)g.nm[0]);
-      label_kernel<ND, MODE, W, R><<<lgrid, 32 * W, 0, st>>>(g, seeds, weights, rec, ridx, rcount, clist, ccount, mask, labels, stats);
+      const cudaLaunchConfig_t cfg = config(lgrid, 32 * W);
+      cudaLaunchKernelEx(&cfg, label_kernel<ND, MODE, W, R>, g, seeds, weights, (const SeedRec*)rec, (const int*)ridx,
+                         (const int*)rcount, (const int*)clist, (const int*)ccount, mask, labels, stats);
     };
     using I1 = std::integral_constant<int, 1>;
     using I2 = std::integral_constant<int, 2>;

@@ -191,10 +191,13 @@ def test_pruned_dft_vs_oracle(sbx_lib, torch_cuda, shape, L, cutoff, path):
         check_scatter_rows(qI, ref, cutoff, last_shell_members(mat, L, cutoff, 1e-12))
 
 
-@pytest.mark.parametrize("shape", [(256, 256, 32), (384, 384, 16), (48, 48, 64), (128, 128, 128), (32, 32, 32)])
+@pytest.mark.parametrize("shape", [(256, 256, 32), (384, 384, 16), (48, 48, 64), (128, 128, 128), (32, 32, 32),
+                                   (64, 64, 128), (128, 128, 256), (256, 256, 128), (192, 192, 384)])
 def test_blocked_pruned_kernel_vs_gather(sbx_lib, torch_cuda, monkeypatch, shape):
-    """pruned_blocked_kernel (the form used for 512^3 / 1024^3 planes and for slabs), forced on grids the oracle and
-    the cuFFT gather path can check: 1-3 row blocks, in-kernel finish with peaks, two fields per launch."""
+    """The row-blocked kernels (the forms used for 512^3 / 1024^3 planes and for slabs), forced on grids the oracle and
+    the cuFFT gather path can check: 1-3 row blocks, in-kernel finish with peaks, two fields per launch.  Grids with
+    N2 % 128 == 0 and blocks of 64 k rows run the bulk-staged kernel (TMA pieces of 1, 2 or 3 segments per half row);
+    it keeps the summation order of the LDG blocked kernel, so the two must agree bit for bit."""
     from simubox_b200 import Scatter
 
     monkeypatch.setenv("SBX_FUSED_BLOCKED", "1")
@@ -204,7 +207,15 @@ def test_blocked_pruned_kernel_vs_gather(sbx_lib, torch_cuda, monkeypatch, shape
     pk = dict(width=0.5, step=500, cutoff=1e9, min_height=0.0)
     out = run_scatter(sbx_lib, torch_cuda, mats, L, 30, 1e-12, FUSED, peaks=pk)
     from simubox_b200.scatter import get_plan
-    assert get_plan(shape, L, 30, 1e-12, max_batch=2, path=FUSED).kernel == "pruned_blocked_kernel"
+    yb_rows = 128 if shape[1] % 128 == 0 else shape[1]
+    bulk = shape[2] % 128 == 0 and yb_rows % 64 == 0
+    assert get_plan(shape, L, 30, 1e-12, max_batch=2, path=FUSED).kernel == ("pruned_bulk_kernel" if bulk else "pruned_blocked_kernel")
+    if bulk:
+        monkeypatch.setenv("SBX_BULK", "0")
+        ldg = run_scatter(sbx_lib, torch_cuda, mats, L, 30, 1e-12, FUSED, peaks=pk)
+        assert get_plan(shape, L, 30, 1e-12, max_batch=2, path=FUSED).kernel == "pruned_blocked_kernel"
+        monkeypatch.delenv("SBX_BULK")
+        assert np.array_equal(out["I"].cpu().numpy(), ldg["I"].cpu().numpy())
     monkeypatch.delenv("SBX_FUSED_BLOCKED")
     ref = run_scatter(sbx_lib, torch_cuda, mats, L, 30, 1e-12, GATHER, peaks=pk)
     a, b = out["I"].cpu().numpy(), ref["I"].cpu().numpy()
@@ -219,7 +230,7 @@ def test_blocked_pruned_kernel_vs_gather(sbx_lib, torch_cuda, monkeypatch, shape
 
 
 def test_giant_grid_uses_the_blocked_kernel(sbx_lib, torch_cuda):
-    """512^3 (1 GB per field): AUTO picks the pruned path with the row-blocked kernel; checked against the cuFFT gather
+    """512^3 (1 GB per field): AUTO picks the pruned path with the row-blocked (bulk-staged) kernel; checked against the cuFFT gather
     path and through size-independent properties (DC row, x4 under x2 scaling)."""
     from simubox_b200 import Scatter, synth
     from simubox_b200.scatter import get_plan
@@ -229,7 +240,7 @@ def test_giant_grid_uses_the_blocked_kernel(sbx_lib, torch_cuda):
     L = synth.box_for(cells)
     f = synth.fields_torch(0, 1, (n, n, n), cells=cells)
     out = Scatter.sacttering_peak_batch(f, L, max_batch=1)
-    assert out["path"] == "pruned_dft_fused" and get_plan((n, n, n), L, 30, 1e-12, max_batch=1).kernel == "pruned_blocked_kernel"
+    assert out["path"] == "pruned_dft_fused" and get_plan((n, n, n), L, 30, 1e-12, max_batch=1).kernel == "pruned_bulk_kernel"
     I = out["I"][0].cpu().numpy()
     ref = Scatter.sacttering_peak_batch(f, L, max_batch=1, path=GATHER)["I"][0].cpu().numpy()
     assert np.all(np.abs(I[:-1] - ref[:-1]) <= 1e-9 * np.abs(ref[:-1]) + 1e-12 * np.abs(ref).max())
