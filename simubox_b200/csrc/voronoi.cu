@@ -122,6 +122,41 @@ __device__ __forceinline__ void resolve_image(const VorGeo& g, const double* __r
   }
 }
 
+// tile_bounds that also returns which periodic image it used, as a code: bits 2a..2a+1 for internal axis a
+// (0 = the seed itself, 1 = p - L, 2 = p + L), bit 6 = `amb`.  The mid kernel parks this byte next to the lower
+// bound, so a seed that survives is not evaluated a second time: its record is fl(p -+ L) per the code.
+template <int ND>
+__device__ __forceinline__ void tile_bounds_code(const VorGeo& g, const double* __restrict__ seeds,
+                                                 const double* __restrict__ weights, long long s, const double c[3],
+                                                 const double h[3], double& LB, double& UB, unsigned& code) {
+  double smin = 0.0, smax = 0.0;
+  code = 0;
+#pragma unroll
+  for (int a = 3 - ND; a < 3; ++a) {
+    const double p0 = seed_coord<ND>(seeds, s, a);
+    double d = (g.mode == 1 ? p0 + (double)s : p0) - c[a];
+    if (g.periodic) {
+      const double L = g.box[a], hL = 0.5 * L;
+      if (d > hL) { d -= L; code |= 1u << (2 * a); }
+      else if (d < -hL) { d += L; code |= 2u << (2 * a); }
+      if (!(fabs(d) + h[a] < hL - 1e-9 * (L + 1.0))) code |= 64u;
+    }
+    const double t = fabs(d);
+    const double dmax = t + h[a], dmin = fmax(t - h[a], 0.0);
+    smin += dmin * dmin;
+    smax += dmax * dmax;
+  }
+  if (g.mode == 1) {
+    const double w = weights ? weights[s] : 0.0;
+    LB = smin - w; UB = smax - w;
+  } else if (weights) {
+    const double w = weights[s];
+    LB = sqrt(smin) - w; UB = sqrt(smax) - w;
+  } else {
+    LB = smin; UB = smax;
+  }
+}
+
 __device__ __forceinline__ bool may_win(double LB, double U) {
   const double slack = 1e-10 * (fabs(U) + fabs(LB) + 1.0);
   return LB - slack <= U + slack;  // never drops a seed that could tie or win
@@ -322,6 +357,7 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
            int* __restrict__ ridx, int* __restrict__ rcount) {
   constexpr int kRounds = 8, kChunk = 32 * kRounds;
   __shared__ double s_lb[4][kChunk];
+  __shared__ unsigned char s_code[4][kChunk];   // image code of every candidate (tile_bounds_code)
   __shared__ alignas(16) SeedRec s_kr[4][kCap];  // records that passed the interval test, per warp
   __shared__ int s_ki[4][kCap];
   const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
@@ -347,6 +383,55 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
   const bool cache = n <= kChunk;
   double best = INFINITY;
   bool amb;
+  int base = 0;
+  bool any_amb = false;
+  if (cache) {
+    // The usual case (a coarse list of <= 256 seeds): one evaluation per candidate.  All seed indices are fetched
+    // first (one dependent load less per round), the lower bound and the image code of every candidate are parked
+    // in shared memory, and the second pass only compares, shifts the coordinates of the survivors and stores.
+    int sid[kRounds];
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      const int i = k * 32 + lane;
+      sid[k] = i < n ? (src ? src[i] : i) : -1;
+    }
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      double LB = INFINITY, UB = INFINITY;
+      unsigned code = 0;
+      if (sid[k] >= 0) tile_bounds_code<ND>(g, seeds, weights, sid[k], c, h, LB, UB, code);
+      best = fmin(best, UB);
+      s_lb[warp][k * 32 + lane] = LB;
+      s_code[warp][k * 32 + lane] = (unsigned char)code;
+    }
+    const double U = warp_min(best);
+#pragma unroll
+    for (int k = 0; k < kRounds; ++k) {
+      if (k * 32 >= n) break;
+      const bool keep = sid[k] >= 0 && may_win(s_lb[warp][k * 32 + lane], U);
+      const unsigned bal = __ballot_sync(kFull, keep);
+      if (keep) {
+        const int slot = base + __popc(bal & ((1u << lane) - 1u));
+        const unsigned code = s_code[warp][k * 32 + lane];
+        any_amb |= (code & 64u) != 0;
+        if (slot < kCap) {
+          double pr[3] = {0.0, 0.0, 0.0};
+#pragma unroll
+          for (int a = 3 - ND; a < 3; ++a) {
+            const double p0 = seed_coord<ND>(seeds, sid[k], a);
+            const unsigned sh = (code >> (2 * a)) & 3u;
+            pr[a] = sh == 1u ? __dsub_rn(p0, g.box[a]) : (sh == 2u ? __dadd_rn(p0, g.box[a]) : p0);
+          }
+          SeedRec r;
+          r.x = pr[0]; r.y = pr[1]; r.z = pr[2];
+          r.w = weights ? weights[sid[k]] : 0.0;
+          s_kr[warp][slot] = r;
+          s_ki[warp][slot] = sid[k];
+        }
+      }
+      base += __popc(bal);
+    }
+  } else {
   for (long long c0 = 0; c0 < n; c0 += kChunk) {
 #pragma unroll 2
     for (int k = 0; k < kRounds; ++k) {
@@ -354,12 +439,9 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
       double LB = INFINITY, UB = INFINITY;
       if (i < n) tile_bounds<ND>(g, seeds, weights, src ? src[i] : i, c, h, LB, UB, amb);
       best = fmin(best, UB);
-      if (cache) s_lb[warp][k * 32 + lane] = LB;
     }
   }
   const double U = warp_min(best);
-  int base = 0;
-  bool any_amb = false;
   for (long long c0 = 0; c0 < n; c0 += kChunk) {
 #pragma unroll 2
     for (int k = 0; k < kRounds; ++k) {
@@ -367,13 +449,11 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
       const long long i = c0 + k * 32 + lane;
       const long long s = i < n ? (src ? src[i] : i) : 0;
       double LB = INFINITY, UB;
-      if (cache) LB = s_lb[warp][k * 32 + lane];
-      else if (i < n) tile_bounds<ND>(g, seeds, weights, s, c, h, LB, UB, amb);
+      if (i < n) tile_bounds<ND>(g, seeds, weights, s, c, h, LB, UB, amb);
       const bool keep = i < n && may_win(LB, U);
       const unsigned bal = __ballot_sync(kFull, keep);
       if (keep) {
         const int slot = base + __popc(bal & ((1u << lane) - 1u));
-        tile_bounds<ND>(g, seeds, weights, s, c, h, LB, UB, amb);
         any_amb |= amb;
         if (slot < kCap) {
           double pr[3];
@@ -387,6 +467,7 @@ mid_kernel(VorGeo g, int n_mid, const double* __restrict__ seeds, const double* 
       }
       base += __popc(bal);
     }
+  }
   }
   const bool generic = __any_sync(kFull, any_amb) || g.mode == 1;
   __syncwarp();
