@@ -9,4 +9,4 @@ for B in 0 1; do
   SBX_BULK=$B timeout 600 python bench.py --workload slab --grid $G --cells 8 --steps 5 --warmup 3 2> $O/bench_slab_${G}_bulk$B.err | grep '^{' | tee $O/bench_slab_${G}_bulk$B.json | python -c "
 import json,sys; d=json.loads(sys.stdin.read()); print('slab $G bulk=$B', d['config']['path'], d['ms_per_step'], d['roofline']['frac'], d['stage_ms'])"
 done; done
-bash scripts/gpu_vor_ab3.sh "SBX_VOR_PDL=0" "SBX_VOR_PDL=1"
+

@@ -77,14 +77,33 @@ __device__ inline void fused_finish(const FusedArgs& A, int field, double* work)
   double* Iu = work + A.n_shells;  // n_umodes (region reused by the peak search afterwards)
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5, nwarp = blockDim.x >> 5;
   const double2* part = A.partial + (long long)field * A.parts * A.n_umodes;
-  for (int u = tid; u < A.n_umodes; u += blockDim.x) {
-    double sr = 0.0, si = 0.0;
-    for (int ch = 0; ch < A.parts; ++ch) {  // fixed order: independent of which CTA produced which unit
-      const double2 p = __ldcg(part + (long long)ch * A.n_umodes + u);
-      sr += p.x;
-      si += p.y;
+  if (A.parts <= 64) {
+    for (int u = tid; u < A.n_umodes; u += blockDim.x) {
+      double sr = 0.0, si = 0.0;
+      for (int ch = 0; ch < A.parts; ++ch) {  // fixed order: independent of which CTA produced which unit
+        const double2 p = __ldcg(part + (long long)ch * A.n_umodes + u);
+        sr += p.x;
+        si += p.y;
+      }
+      Iu[u] = A.factor * (sr * sr + si * si);
     }
-    Iu[u] = A.factor * (sr * sr + si * si);
+  } else {
+    // many units per field (giant grids): a warp per mode, lane l adds units l, l + 32, ... in order and a fixed
+    // shuffle tree adds the lanes -- still independent of the schedule, with 32 loads in flight instead of one
+    for (int u = warp; u < A.n_umodes; u += nwarp) {
+      double sr = 0.0, si = 0.0;
+      for (int ch = lane; ch < A.parts; ch += 32) {
+        const double2 p = __ldcg(part + (long long)ch * A.n_umodes + u);
+        sr += p.x;
+        si += p.y;
+      }
+#pragma unroll
+      for (int o = 16; o > 0; o >>= 1) {
+        sr += __shfl_xor_sync(0xffffffffu, sr, o);
+        si += __shfl_xor_sync(0xffffffffu, si, o);
+      }
+      if (lane == 0) Iu[u] = A.factor * (sr * sr + si * si);
+    }
   }
   __syncthreads();
   for (int s = warp; s < A.n_shells; s += nwarp) {
@@ -362,17 +381,23 @@ pruned_blocked_kernel(const FusedArgs A) {
   }
 }
 
-// slab path: sums[mode] = sum over this rank's units in fixed order (one thread per mode)
+// slab path: sums[mode] = sum over this rank's units in fixed order (one warp per mode: lane l adds units l, l + 32, ...
+// in order, then a fixed shuffle tree)
 __global__ void fused_reduce_parts_kernel(const double2* __restrict__ partial, int parts, int n_umodes, double2* __restrict__ sums) {
-  const int u = blockIdx.x * blockDim.x + threadIdx.x;
+  const int u = (blockIdx.x * blockDim.x + threadIdx.x) >> 5, lane = threadIdx.x & 31;
   if (u >= n_umodes) return;
   double sr = 0.0, si = 0.0;
-  for (int p = 0; p < parts; ++p) {
+  for (int p = lane; p < parts; p += 32) {
     const double2 v = partial[(long long)p * n_umodes + u];
     sr += v.x;
     si += v.y;
   }
-  sums[u] = make_double2(sr, si);
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    sr += __shfl_xor_sync(0xffffffffu, sr, o);
+    si += __shfl_xor_sync(0xffffffffu, si, o);
+  }
+  if (lane == 0) sums[u] = make_double2(sr, si);
 }
 
 // slab path: shell sums (+ peaks) from mode sums that are already complete (A.partial = sums, A.parts = 1)
@@ -633,8 +658,9 @@ pruned_ring_kernel(const FusedArgs A) {
 // the segments of a row group.  Stage layout: pieces of even rows | 64 B | pieces of odd rows, so that the two
 // rows a quarter-warp reads with one 16-byte load per lane fall into disjoint banks.
 // One CTA of 8 warps per SM: 2 x 8 x 8.06 KB of stages + the z twiddles (N2 x 64 B) + the unit's work area.
-// Requires N2 % 128 == 0 and yb_rows % 64 == 0.  Same unit / partial-sum / finish scheme, hence the same bits,
-// as pruned_blocked_kernel.
+// Requires N2 % 128 == 0, yb_rows % 64 == 0 and at least two items per unit.  Same unit / partial-sum / finish
+// scheme, hence (for the same planes per unit) the same bits, as pruned_blocked_kernel.  A CTA knows its next unit
+// one unit ahead, and the item sequence of a warp runs on into it: no pipeline bubble between units.
 // ------------------------------------------------------------------------------------------
 constexpr int kBulkSeg = 64;                                  // doubles per piece
 constexpr int kBulkPiece = kBulkSeg * 8;                      // 512 bytes
@@ -658,7 +684,7 @@ pruned_bulk_kernel(const FusedArgs A) {
   double* gT = work;                                  // 16 * gstride
   double* c2 = gT + (size_t)16 * gstride;             // 256
   double* hp = c2 + 256;                              // 256
-  __shared__ int s_unit, s_last;
+  __shared__ int s_units[2], s_last;  // units k and k + 1 of this CTA (k & 1): the pipeline runs one unit ahead
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   for (int i = tid; i < A.ds * 128; i += 256) twf[i] = A.twf[i];
   if (tid < 8 * kBulkStages) pf_mbar_init(&bars[tid], 1);
@@ -688,28 +714,44 @@ pruned_bulk_kernel(const FusedArgs A) {
   const int put_off = bulk_piece_offset(lane & 7, (lane >> 3) & 1);
   const long long put_src = (long long)(lane & 7) * A.N2 + (long long)((lane >> 3) & 1) * (A.N2 >> 1);
   unsigned it = 0;  // items this warp has consumed so far (all units): stage = it % 2, parity = (it / 2) % 2
+  if (tid == 0) {
+    s_units[0] = (int)atomicAdd(&A.ctrl[0], 1u);
+    s_units[1] = (int)atomicAdd(&A.ctrl[0], 1u);
+  }
   __syncthreads();
+  // first row of unit u (nullptr past the end)
+  auto unit_rows = [&](int u) -> const double* {
+    if (u >= n_units) return nullptr;
+    const int f = u / A.parts, pt = u - f * A.parts;
+    const int ch = pt / A.yblocks, b = pt - ch * A.yblocks;
+    return A.fields + ((long long)f * A.planes + (long long)ch * A.xc) * plane_doubles + (long long)b * A.yb_rows * A.N2;
+  };
 
-  for (;;) {
-    if (tid == 0) s_unit = (int)atomicAdd(&A.ctrl[0], 1u);
-    __syncthreads();
-    const int unit = s_unit;
+  for (int k = 0;; ++k) {
+    const int unit = s_units[k & 1];
     if (unit >= n_units) break;
     const int field = unit / A.parts, part = unit - field * A.parts;
     const int chunk = part / A.yblocks, yb = part - chunk * A.yblocks;
     const int x0 = chunk * A.xc;
-    const double* ubase = A.fields + ((long long)field * A.planes + x0) * plane_doubles + (long long)yb * A.yb_rows * A.N2;
-    // request item i of this unit into stage st (whole warp)
+    const double* ubase = unit_rows(unit);
+    const double* nbase = unit_rows(s_units[(k + 1) & 1]);  // the CTA's next unit: its first two items are requested
+                                                             // while this unit finishes (n_items >= 2)
+    // request item i into stage st (whole warp); items n_items, n_items + 1 are items 0, 1 of the next unit
     auto issue = [&](int i, int st) {
+      const double* ub = ubase;
+      if (i >= n_items) { ub = nbase; i -= n_items; }
+      if (!ub) return;
       const int sg = i % nseg, t2 = i / nseg;
       const int gi = t2 % gpw, xi = t2 / gpw;
-      const double* src = ubase + (long long)xi * plane_doubles + (long long)((warp + 8 * gi) * 8) * A.N2 + sg * kBulkSeg;
+      const double* src = ub + (long long)xi * plane_doubles + (long long)((warp + 8 * gi) * 8) * A.N2 + sg * kBulkSeg;
       if (lane == 0) pf_mbar_expect_tx(&my_bars[st], 16 * kBulkPiece);
       __syncwarp();
       if (lane < 16) pf_bulk_g2s(my_stages + (size_t)st * kBulkStageBytes + put_off, src + put_src, kBulkPiece, &my_bars[st]);
     };
-    issue(0, it & 1u);
-    if (n_items > 1) issue(1, (it + 1u) & 1u);
+    if (k == 0) {  // later units find their first two items already requested
+      issue(0, it & 1u);
+      issue(1, (it + 1u) & 1u);
+    }
     double fr[kFusedModesPerThread], fi[kFusedModesPerThread];
     int jj[kFusedModesPerThread];
 #pragma unroll
@@ -739,7 +781,7 @@ pruned_bulk_kernel(const FusedArgs A) {
           }
           __syncwarp();
           asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-          if (item + 2 < n_items) issue(item + 2, st);
+          issue(item + 2, st);
         }
         const int y = (warp + 8 * gi) * 8 + m;
         gT[(size_t)re0 * gstride + y] = e0;
@@ -792,6 +834,7 @@ pruned_bulk_kernel(const FusedArgs A) {
         fused_finish(A, field, work);
       }
     }
+    if (tid == 0) s_units[k & 1] = (int)atomicAdd(&A.ctrl[0], 1u);  // unit k + 2 (everyone read unit k's slot long ago)
     __syncthreads();
   }
 }

@@ -111,6 +111,7 @@ struct sbx_scatter_plan {
   double2* d_partial = nullptr;
   unsigned* d_ctrl = nullptr;
   int fused_xc = 1;
+  size_t partial_units = 0;  // capacity of d_partial in work units (all fields of one launch)
   cudaStream_t s_aux = nullptr;
   cudaEvent_t ev_planes[2] = {nullptr, nullptr}, ev_finish[2] = {nullptr, nullptr};
   std::map<int, cufftHandle> fft;  // batch -> plan
@@ -460,7 +461,11 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
     }
   }
   else if (path == SBX_SCATTER_PRUNED_FUSED) {
-    const size_t parts = (size_t)g.N0 / p->fused_xc * (p->blocked_ok ? p->yblocks : 1);
+    // giant planes (>= 512^2: the row-blocked kernels) get room for one-plane units, so that a single field or a slab of
+    // it still splits into several units per SM (blocked_unit_planes)
+    const bool giant = p->blocked_ok && (long long)g.N1 * g.N2 >= 512LL * 512LL;
+    const size_t parts = (size_t)g.N0 / (giant ? 1 : p->fused_xc) * (p->blocked_ok ? p->yblocks : 1);
+    p->partial_units = (size_t)p->chunk * parts;
     e = cudaMalloc((void**)&p->d_partial, (size_t)p->chunk * parts * std::max(p->n_umodes, 1) * sizeof(double2));
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_modesum, (size_t)std::max(p->n_umodes, 1) * sizeof(double2));
     if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_ctrl, ((size_t)p->chunk + 1) * sizeof(unsigned));
@@ -545,7 +550,7 @@ static int check_peaks_args(int n, int step, int max_peaks) {
   return SBX_OK;
 }
 
-namespace sbx { static int blocked_unit_planes(const sbx_scatter_plan* p, int n_fields, int planes); }
+namespace sbx { static int blocked_unit_planes(const sbx_scatter_plan* p, bool bulk, int planes); }
 
 // The bulk-staged form of the blocked kernel (pruned_bulk_kernel) applies when rows split into 512-byte pieces per
 // half (N2 % 128 == 0), a block of rows gives every warp whole row groups (yb_rows % 64 == 0) and the stages, the z
@@ -554,7 +559,8 @@ namespace sbx { static int blocked_unit_planes(const sbx_scatter_plan* p, int n_
 static bool bulk_applies(const sbx_scatter_plan* p, size_t bwork) {
   const char* e = getenv("SBX_BULK");
   if (e && atoi(e) == 0) return false;
-  return p->grid.N2 % 128 == 0 && p->yb_rows % 64 == 0 && bulk_smem_bytes(p->grid.N2, bwork) <= kMaxTmaSmem;
+  const bool two_items = (p->yb_rows / 64) * (p->grid.N2 / 128) >= 2 || p->fused_xc >= 2;  // per warp and unit
+  return p->grid.N2 % 128 == 0 && p->yb_rows % 64 == 0 && two_items && bulk_smem_bytes(p->grid.N2, bwork) <= kMaxTmaSmem;
 }
 
 // scatter (+ optional fused peaks) on `batch` device-resident fields
@@ -588,13 +594,13 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
     const bool whole_plane_thin = fused_smem_bytes(g.N0, g.N1, g.N2, fused_work_doubles(g.N1, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks)) > 113 * 1024;
     if ((!p->fused_ok || force_blocked || whole_plane_thin) && p->blocked_ok) {
       A.yb_rows = p->yb_rows; A.yblocks = p->yblocks;
-      A.xc = blocked_unit_planes(p, std::min(p->chunk, batch), g.N0);
-      A.chunks = g.N0 / A.xc; A.parts = A.chunks * A.yblocks;
       const size_t bwork = blocked_work_doubles(p->yb_rows, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks);
+      const bool bulk = bulk_applies(p, bwork);
+      A.xc = blocked_unit_planes(p, bulk, g.N0);
+      A.chunks = g.N0 / A.xc; A.parts = A.chunks * A.yblocks;
       A.work_doubles = (int)bwork;
       const size_t bsmem = blocked_smem_bytes(g.N0, g.N2, bwork);
       if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
-      const bool bulk = bulk_applies(p, bwork);
       p->last_kernel = bulk ? "pruned_bulk_kernel" : "pruned_blocked_kernel";
       for (int c0 = 0; c0 < batch; c0 += p->chunk) {
         const int nb = std::min(p->chunk, batch - c0);
@@ -793,10 +799,21 @@ extern "C" int sbx_scatter_plan_get_profile(sbx_scatter_plan* plan, double* tran
 // ---- pruned-DFT slab helpers (scatter_types.h) --------------------------------------------------
 namespace sbx {
 
-// planes per unit of the blocked kernel.  Fixed per plan: the summation order, hence the bits of the result, must not
-// depend on how many fields a launch carries.  (Halving it for single-field launches to smooth the last wave was
-// measured slower: 0.62 vs 0.46 ms for one 512^3 field -- the per-unit epilogue outweighs the tail.)
-static int blocked_unit_planes(const sbx_scatter_plan* p, int, int) { return p->fused_xc; }
+// Planes per unit of the row-blocked kernels.  Fixed per plan and plane count: the summation order, hence the bits of
+// the result, must not depend on how many fields a launch carries.  The LDG kernel keeps fused_xc (halving it for
+// single-field launches was measured slower: its per-unit epilogue outweighs the tail).  The bulk-staged kernel runs
+// one CTA per SM and pipelines across units, so small units cost nothing: planes per unit are halved until a field
+// (or a rank's slab of it) gives every SM about six units -- as far as the partial-sum buffer of the plan allows
+// (giant planes get room for one-plane units) and every warp keeps two pipeline items per unit.
+static int blocked_unit_planes(const sbx_scatter_plan* p, bool bulk, int planes) {
+  int xc = p->fused_xc;
+  if (!bulk) return xc;
+  const long long per_plane_items = (long long)(p->yb_rows / 64) * (p->grid.N2 / 128);
+  while (xc % 2 == 0 && (long long)(planes / xc) * p->yblocks < 6LL * p->sm_count &&
+         (size_t)p->chunk * (size_t)(p->grid.N0 / (xc / 2)) * p->yblocks <= p->partial_units && (xc / 2) * per_plane_items >= 2)
+    xc /= 2;
+  return xc;
+}
 
 static void slab_args(const sbx_scatter_plan* p, FusedArgs& A) {
   const GridDev& g = p->grid;
@@ -825,20 +842,20 @@ int scatter_slab_partial(sbx_scatter_plan* p, const double* slab, int planes, in
   FusedArgs A;
   slab_args(p, A);
   A.fields = slab; A.n_fields = 1; A.planes = planes; A.x_base = x_base; A.finish = 0;
-  A.xc = blocked_unit_planes(p, 1, planes);
-  A.chunks = planes / A.xc; A.parts = A.chunks * A.yblocks;
   const size_t bwork = blocked_work_doubles(p->yb_rows, A.n_shells, p->n_umodes, 0, false);
+  const bool bulk = bulk_applies(p, bwork);
+  A.xc = blocked_unit_planes(p, bulk, planes);
+  A.chunks = planes / A.xc; A.parts = A.chunks * A.yblocks;
   A.work_doubles = (int)bwork;
   const size_t bsmem = blocked_smem_bytes(A.N0, A.N2, bwork);
   if (bsmem > kMaxDynSmem) return fail(SBX_EINVAL, "blocked pruned kernel needs %zu bytes of shared memory", bsmem);
   SBX_CUDA(cudaMemsetAsync(p->d_ctrl, 0, 2 * sizeof(unsigned), st));
   const int grid = (int)std::min<long long>(A.parts, (long long)p->pruned_ctas_per_sm * p->sm_count);
-  const bool bulk = bulk_applies(p, bwork);
   if (bulk) pruned_bulk_kernel<<<(int)std::min<long long>(A.parts, p->sm_count), 256, bulk_smem_bytes(A.N2, bwork), st>>>(A);
   else if (blocked_twf_in_smem(A.N2)) pruned_blocked_kernel<true><<<grid, 256, bsmem, st>>>(A);
   else pruned_blocked_kernel<false><<<grid, 256, bsmem, st>>>(A);
   SBX_CUDA(cudaGetLastError());
-  fused_reduce_parts_kernel<<<(p->n_umodes + 127) / 128, 128, 0, st>>>(p->d_partial, A.parts, p->n_umodes, modesum);
+  fused_reduce_parts_kernel<<<(p->n_umodes + 3) / 4, 128, 0, st>>>(p->d_partial, A.parts, p->n_umodes, modesum);
   SBX_CUDA(cudaGetLastError());
   p->own_launches += 2;
   p->last_kernel = bulk ? "pruned_bulk_kernel" : "pruned_blocked_kernel";
