@@ -484,7 +484,7 @@ def run_slab(args):
     # pruned DFT: the field is read once.  slab FFT: field + write/read of the half spectrum through the 2D stage,
     # the exchange buffers and the 1D stage, then the scan
     bytes_field = 8 * n ** 3 if pruned else 8 * n ** 3 + 6 * spec
-    kern = "pruned_blocked_kernel" if pruned else "cuFFT 2D + slab_pack_kernel + cuFFT 1D + shell_histogram_kernel"
+    kern = (slab.kernel or "pruned_blocked_kernel") if pruned else "cuFFT 2D + slab_pack_kernel + cuFFT 1D + shell_histogram_kernel"
     comm = "all-reduce of the mode sums (no all-to-all)" if pruned else "NCCL all-to-all (send/recv group) + all-reduce"
     print(json.dumps({
         "metric": "density fields/sec (I(q), one slab-decomposed field)", "value": 1.0 / (ms * 1e-3), "unit": "fields/s",
@@ -496,7 +496,8 @@ def run_slab(args):
         "stage_ms": prof, "n_shells": int(slab.n_shells), "dc_row": float(I[0]),
         "roofline": {"bound": "hbm", "kernel": kern,
                      "achieved": bytes_field / world / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": bytes_field / world / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
+                     "frac": bytes_field / world / (ms * 1e-3) / 1e9 / peak,
+                     "traffic": measured_traffic(f"{kern}|{n}^3|{world} slab(s)"), "peak_source": peak_src,
                      "algorithmic_bytes_per_field": bytes_field},
         "gpu_launches": (3 if pruned else 2) * args.steps, "clocks": clk.summary(),
     }))

@@ -179,6 +179,9 @@ int sbx_scatter_slab_execute(sbx_slab_plan* plan, const double* local_slab, doub
  * to the mode sums, one small all-reduce, no all-to-all), SBX_SCATTER_FFT_DENSE for the slab FFT.  The
  * environment variable SBX_SLAB_PATH=fft|pruned forces one at plan creation. */
 int sbx_scatter_slab_path(const sbx_slab_plan* plan);
+/* dominant hand-written kernel of the last execute in pruned mode ("pruned_bulk_kernel" / "pruned_blocked_kernel"),
+ * "" in slab FFT mode or before the first execute */
+const char* sbx_scatter_slab_kernel(const sbx_slab_plan* plan);
 int sbx_scatter_slab_set_profiling(sbx_slab_plan* plan, int enable);
 int sbx_scatter_slab_profile(sbx_slab_plan* plan, double* ms4_host);
 int sbx_scatter_slab_plan_destroy(sbx_slab_plan* plan);

@@ -26,6 +26,7 @@ _vp = C.c_void_p
 _SIGNATURES = {
     "sbx_version": (C.c_int, []),
     "sbx_scatter_slab_path": (C.c_int, [_vp]),
+    "sbx_scatter_slab_kernel": (C.c_char_p, [_vp]),
     "sbx_particle_splat": (C.c_int, [C.c_int, _vp, _vp, C.c_int64, C.c_int, _i64p, _f64p, C.c_double, _vp, _vp]),
     "sbx_domain_centres": (C.c_int, [C.c_int, C.c_int, _i64p, _vp, C.c_double, C.c_int, _vp, C.c_int64, _vp, _vp, _i64p, _vp]),
     "sbx_cell_stats": (C.c_int, [C.c_int, C.c_int, _i64p, _vp, _vp, C.c_int64, C.c_int, _vp, _vp, _vp, _vp, _vp]),

@@ -396,6 +396,10 @@ extern "C" int sbx_scatter_slab_execute(sbx_slab_plan* p, const double* local_sl
   return SBX_OK;
 }
 
+extern "C" const char* sbx_scatter_slab_kernel(const sbx_slab_plan* p) {
+  return p && p->inner ? sbx_scatter_plan_kernel(p->inner) : "";
+}
+
 extern "C" int sbx_scatter_slab_path(const sbx_slab_plan* p) {
   if (!p) return SBX_EINVAL;
   return p->pruned ? SBX_SCATTER_PRUNED_FUSED : SBX_SCATTER_FFT_DENSE;

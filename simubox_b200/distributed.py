@@ -150,6 +150,11 @@ class SlabScatter:
         # 4: pruned DFT (mode sums + one small all-reduce); 1: slab FFT with all-to-all.  SBX_SLAB_PATH=fft|pruned forces one.
         self.path = int(L_.sbx_scatter_slab_path(self._h))
 
+    @property
+    def kernel(self) -> str:
+        """Dominant hand-written kernel of the last execute in pruned mode ('' in slab FFT mode)."""
+        return (_lib.lib().sbx_scatter_slab_kernel(self._h) or b"").decode()
+
     def execute(self, local_slab, out=None):
         """``local_slab``: CUDA fp64 tensor (N0/world, N1, N2) = this rank's planes.  Returns the
         (n_shells,) CUDA tensor of shell intensities (identical on every rank); asynchronous on
