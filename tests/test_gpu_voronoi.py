@@ -67,6 +67,30 @@ def test_mask_and_weights_forms(sbx_lib):
         VoronoiCell.label_grid(pts, 0, shape=(20, 20, 20), method="nope")
 
 
+@pytest.mark.parametrize("shape,weights,periodic", [((40, 24, 48), 0, True), ((16, 8, 16), 0, False), ((36, 20, 32), 0.75, True),
+                                                    ((33, 17, 64), 0, True), ((32, 32, 24), 0, True)])
+def test_sparse_blob_masks(sbx_lib, shape, weights, periodic):
+    """Blob masks that leave most of the grid dead (whole label CTAs and warp tiles without a live voxel, boxes with a
+    single live voxel, ragged grid edges, unaligned mask columns) against the oracle, and an all-dead mask."""
+    from simubox_b200 import VoronoiCell
+
+    rng = np.random.default_rng(sum(shape))
+    pts = rng.uniform(0, 1, (40, 3)) * np.array(shape)
+    idx = np.indices(shape)
+    mask = np.zeros(shape, dtype=bool)
+    for _ in range(4):  # a few blobs, most of the grid stays dead
+        c = rng.uniform(0, 1, 3) * np.array(shape)
+        mask |= sum((idx[a] - c[a]) ** 2 for a in range(3)) < rng.uniform(9, 36)
+    mask[shape[0] - 1, shape[1] - 1, shape[2] - 1] = True   # one live voxel in the last (ragged) box
+    mask[0, 0, 7] = True
+    box = tuple(float(v) for v in shape) if periodic else None
+    lab = VoronoiCell.label_grid(pts, weights, shape=shape, box=box, mask=mask)
+    ref = voronoi_np.label_grid(pts, weights, shape, box=box, mask=mask)
+    assert np.array_equal(lab, ref) and (lab[~mask] == -1).all() and (lab[mask] >= 0).all()
+    empty = np.zeros(shape, dtype=bool)
+    assert (VoronoiCell.label_grid(pts, weights, shape=shape, box=box, mask=empty) == -1).all()
+
+
 def test_baseline_config_256_cubed_4096_seeds(sbx_lib):
     """BASELINE config 3: 256^3, 4096 jittered-lattice seeds, periodic, masked.  The reference loop
     needs ~13 min there, so parity is on 2^14 random voxels + the 16^3 corner block (wrap-around),
