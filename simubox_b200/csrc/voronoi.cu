@@ -830,8 +830,9 @@ static void launch_voronoi(const VorGeo& g, long long ctiles, long long tiles, c
     const cudaLaunchConfig_t cfg = config(dim3((unsigned)((tiles + 3) / 4)), 128);
     cudaLaunchKernelEx(&cfg, mid_kernel<ND>, g, (int)tiles, seeds, weights, (const int*)clist, (const int*)ccount, rec, ridx, rcount);
   }
-  // (warps per CTA, warp tiles per warp).  Measured at 256^3 / 4096 seeds: (8,1) 0.124 ms, (4,1) 0.110 ms, (4,2) 0.118,
-  // (4,4) 0.121, (2,8) 0.126: small CTAs recycle their SM slot sooner; more rounds per warp cost registers.
+  // (warps per CTA, warp tiles per warp).  Measured at 256^3 / 4096 seeds (whole labelling, r01 v6): (8,1) 0.097 ms,
+  // (4,1) 0.089 ms, (4,2) 0.101, (2,8) 0.105 (v5: 0.124 / 0.110 / 0.118 / 0.126): small CTAs recycle their SM slot
+  // sooner; more rounds per warp cost registers.
   static const int lw = [] { const char* e = getenv("SBX_LABEL_WARPS"); const int v = e ? atoi(e) : 4; return v == 2 || v == 8 ? v : 4; }();
   static const int lr = [] { const char* e = getenv("SBX_LABEL_ROUNDS"); return e ? atoi(e) : 1; }();
   auto launch_label = [&](auto mode_tag) {
