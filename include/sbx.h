@@ -141,7 +141,8 @@ int sbx_voronoi_label(int device, int ndim, const int64_t* N, const double* seed
                       const double* weights, int mode, const double* box_host,
                       const uint8_t* mask, int32_t* labels, void* stream, int64_t* stats_host);
 /* Plan form of the same call for repeated labellings of one grid size (sweeps): the plan owns the
- * candidate-list workspace, execute is three kernel launches, asynchronous on `stream` unless
+ * workspace (cell table + sorted image points, or the tile candidate lists when weights / power mode are used),
+ * execute is three kernel launches, asynchronous on `stream` unless
  * stats_host is non-NULL.  A plan is bound to one device; executes on one plan must be issued in
  * stream order (the workspace is reused). */
 typedef struct sbx_voronoi_plan sbx_voronoi_plan;
@@ -150,6 +151,15 @@ int sbx_voronoi_plan_execute(sbx_voronoi_plan* plan, const double* seeds, int64_
                              const double* weights, int mode, const double* box_host,
                              const uint8_t* mask, int32_t* labels, void* stream,
                              int64_t* stats_host);
+/* The same labelling restricted to the planes [x_lo, x_hi) of the first grid axis -- the voxel-slab
+ * decomposition of one grid across GPUs (seeds replicated, planes [r N0/P, (r+1) N0/P) on
+ * rank r, no collective; replaces the same loop, voronoi.py:284-292, over that rank's pixels).
+ * `labels` and `mask` point to the first plane of the range ((x_hi - x_lo) x N1 [x N2] elements); the
+ * result equals the corresponding planes of a whole-grid labelling bit for bit. */
+int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* plan, const double* seeds, int64_t S,
+                                   const double* weights, int mode, const double* box_host,
+                                   const uint8_t* mask, int32_t* labels, int64_t x_lo, int64_t x_hi,
+                                   void* stream, int64_t* stats_host);
 int sbx_voronoi_plan_destroy(sbx_voronoi_plan* plan);
 
 /* ---- one giant field across GPUs: slab-decomposed FFT + NCCL all-to-all ---------------

@@ -5,6 +5,9 @@ Two cases:
 * batches / sweeps of independent fields -- ``shard_range`` / ``shard_indices`` give each rank its
   fields, ``gather_rows`` brings the small per-field results to every rank.  No data-path
   collective.
+* one Voronoi grid -- ``label_grid_sharded``: seeds replicated, rank r labels the planes ``shard_range(N0, r, P)``
+  of axis 0 (``sbx_voronoi_plan_execute_range``); labels stay sharded, ``gather_planes`` all-gathers them if a full
+  copy is wanted.  No collective in the labelling itself.
 * one giant field -- ``SlabScatter`` owns an NCCL communicator created by libsimubox_b200.so
   (``sbx_nccl_unique_id`` on rank 0, broadcast through the existing process group,
   ``sbx_nccl_comm_create`` everywhere) and runs the slab-decomposed FFT with an all-to-all
@@ -88,6 +91,62 @@ def gather_rows(local_rows: np.ndarray, indices: Sequence[int], total: int) -> n
         i = i.cpu().numpy()
         keep = i >= 0
         out[i[keep]] = r.cpu().numpy()[keep]
+    return out
+
+
+def label_grid_sharded(points, weights=0, shape: Sequence[int] = (256, 256, 256), method="additive", box=None, mask=None,
+                       device: int | None = None, gather: bool = False, rank: int | None = None, world: int | None = None):
+    """Voronoi labelling of ONE grid spread over the ranks by voxel slab (the loop it replaces is
+    SimuBox/calculator/voronoi.py:284-292, split over the first pixel coordinate).  Every rank passes the complete
+    ``points`` (and ``weights``); ``mask`` may be the whole-grid mask or this rank's planes.  Returns
+    ``(labels_local, (x_lo, x_hi))`` with ``labels_local`` a CUDA int32 tensor of shape ``(x_hi - x_lo, *shape[1:])``;
+    with ``gather=True`` the full ``shape`` array (numpy) on every rank instead of the local tensor."""
+    from .voronoi import VoronoiCell
+
+    r, w = rank_world()
+    rank = r if rank is None else int(rank)
+    world = w if world is None else int(world)
+    dev = int(device if device is not None else os.environ.get("LOCAL_RANK", "0"))
+    lo, hi = shard_range(int(shape[0]), rank, world)
+    if hi <= lo:
+        raise ValueError(f"rank {rank} of {world} owns no plane of a grid with {shape[0]} planes")
+    local = VoronoiCell.label_grid(points, weights, shape=shape, method=method, box=box, mask=mask, device=dev,
+                                   return_tensor=True, planes=(lo, hi))
+    if not gather:
+        return local, (lo, hi)
+    return gather_planes(local.cpu().numpy(), (lo, hi), tuple(int(n) for n in shape)), (lo, hi)
+
+
+def gather_planes(local: np.ndarray, planes: Tuple[int, int], shape: Sequence[int]) -> np.ndarray:
+    """All-gather the plane slabs of a sharded grid into the full array on every rank (any backend; identity
+    without a process group).  Slabs may differ by one plane (``shard_range``): they are padded to the largest."""
+    import torch
+    import torch.distributed as dist
+
+    shape = tuple(int(n) for n in shape)
+    local = np.ascontiguousarray(local)
+    lo, hi = int(planes[0]), int(planes[1])
+    if tuple(local.shape) != (hi - lo,) + shape[1:]:
+        raise ValueError(f"slab shape {local.shape} does not match planes {planes} of {shape}")
+    out = np.empty(shape, dtype=local.dtype)
+    if not (dist.is_available() and dist.is_initialized()) or dist.get_world_size() == 1:
+        if (lo, hi) != (0, shape[0]):
+            raise ValueError("a single process must hold every plane")
+        out[:] = local
+        return out
+    world = dist.get_world_size()
+    per = (shape[0] + world - 1) // world
+    dev = torch.device("cuda", torch.cuda.current_device()) if dist.get_backend() == "nccl" else torch.device("cpu")
+    buf = torch.zeros((per,) + shape[1:], dtype=torch.from_numpy(local).dtype, device=dev)
+    buf[:hi - lo] = torch.from_numpy(local).to(dev)
+    span = torch.tensor([lo, hi], dtype=torch.int64, device=dev)
+    bufs = [torch.empty_like(buf) for _ in range(world)]
+    spans = [torch.empty_like(span) for _ in range(world)]
+    dist.all_gather(bufs, buf)
+    dist.all_gather(spans, span)
+    for b, sp in zip(bufs, spans):
+        a, e = (int(v) for v in sp.cpu().tolist())
+        out[a:e] = b[:e - a].cpu().numpy()
     return out
 
 

@@ -77,18 +77,28 @@ class VoronoiCell:
     @classmethod
     def label_grid(cls, points, weights=0, shape: Sequence[int] = (500, 500),
                    method: Union[WeightedMode, str] = WeightedMode.ADDITIVE, box: Optional[Sequence[float]] = None,
-                   mask=None, device: int = 0, return_tensor: bool = False, stats: bool = False):
+                   mask=None, device: int = 0, return_tensor: bool = False, stats: bool = False,
+                   planes: Optional[Tuple[int, int]] = None):
         """Label every voxel of ``product(range(shape[0]), range(shape[1])[, range(shape[2])])``
         with the index of the seed minimising ``method`` (first minimum, like ``np.argmin``).
 
         ``box``: periodic box lengths in voxel units (minimum image), None = non-periodic as the
         reference.  ``mask``: uint8/bool array of ``shape``; voxels where it is 0 get label -1.
+        ``planes=(x_lo, x_hi)``: label only those planes of the first axis (one rank's slab of a grid
+        sharded across GPUs, see ``distributed.label_grid_sharded``); the result then has shape
+        ``(x_hi - x_lo, *shape[1:])`` and ``mask`` may be the whole-grid mask or the slab's.
         Returns an int32 array of ``shape`` (numpy, or a CUDA tensor with ``return_tensor``);
         with ``stats=True`` also a dict(evaluations, tiles, overflow_tiles).
         """
         torch = torch_cuda()
         shape = tuple(int(n) for n in shape)
         nd = len(shape)
+        if not isinstance(points, torch.Tensor) and not np.isfinite(np.asarray(points, dtype=np.float64)).all():
+            raise ValueError("seed coordinates must be finite")
+        x_lo, x_hi = (0, shape[0]) if planes is None else (int(planes[0]), int(planes[1]))
+        if not (0 <= x_lo < x_hi <= shape[0]):
+            raise ValueError(f"planes {planes} outside [0, {shape[0]})")
+        local = (x_hi - x_lo,) + shape[1:]
         pts = to_device(np.ascontiguousarray(points, dtype=np.float64) if not isinstance(points, torch.Tensor) else points,
                         device, torch.float64)
         if pts.ndim != 2 or pts.shape[1] != nd:
@@ -105,10 +115,13 @@ class VoronoiCell:
         m = None
         if mask is not None:
             m = to_device(mask if isinstance(mask, torch.Tensor) else np.ascontiguousarray(mask), device)
-            m = (m != 0).to(torch.uint8).contiguous() if m.dtype != torch.uint8 else m
-            if tuple(m.shape) != shape:
+            m = (m != 0).to(torch.uint8) if m.dtype != torch.uint8 else m
+            if tuple(m.shape) == shape:
+                m = m[x_lo:x_hi]
+            elif tuple(m.shape) != local:
                 raise ValueError(f"mask shape {tuple(m.shape)} != grid {shape}")
-        labels = torch.empty(shape, dtype=torch.int32, device=pts.device)
+            m = m.contiguous()
+        labels = torch.empty(local, dtype=torch.int32, device=pts.device)
         pb = None
         if box is not None:
             _keep, pb = _lib.f64(box)
@@ -116,8 +129,8 @@ class VoronoiCell:
                 raise ValueError(f"box must have {nd} entries")
         st_arr = np.zeros(3, dtype=np.int64) if stats else None
         plan = _get_plan(device, shape)
-        _lib.check(_lib.lib().sbx_voronoi_plan_execute(
-            plan._h, ptr(pts), S, ptr(w), _mode_id(method), pb, ptr(m), ptr(labels), stream_ptr(device),
+        _lib.check(_lib.lib().sbx_voronoi_plan_execute_range(
+            plan._h, ptr(pts), S, ptr(w), _mode_id(method), pb, ptr(m), ptr(labels), x_lo, x_hi, stream_ptr(device),
             st_arr.ctypes.data_as(C.POINTER(C.c_int64)) if stats else None))
         out = labels if return_tensor else labels.cpu().numpy()
         if stats:

@@ -73,3 +73,47 @@ def test_gloo_world2_sweep_gather(total):
     want = np.stack([i, i ** 2, i % 2], axis=1)
     for rank in (0, 1):
         assert np.array_equal(got[rank], want), f"rank {rank} sees a different gathered table"
+
+
+def _planes_worker(rank, world, port, shape, q):
+    import torch.distributed as dist
+
+    os.environ.update(MASTER_ADDR="127.0.0.1", MASTER_PORT=str(port), RANK=str(rank), WORLD_SIZE=str(world))
+    dist.init_process_group("gloo", rank=rank, world_size=world)
+    try:
+        lo, hi = D.shard_range(shape[0], rank, world)
+        # stand-in for the labels of this rank's planes: value = global linear voxel index
+        full = np.arange(int(np.prod(shape)), dtype=np.int32).reshape(shape)
+        q.put((rank, D.gather_planes(full[lo:hi].copy(), (lo, hi), shape)))
+    finally:
+        dist.destroy_process_group()
+
+
+@pytest.mark.parametrize("shape", [(7, 3, 5), (8, 6)])
+def test_gloo_world2_voxel_slab_gather(shape):
+    """Partition logic of the sharded Voronoi labelling (uneven plane counts included): every rank ends up with
+    the whole label grid."""
+    import torch.multiprocessing as mp
+
+    ctx = mp.get_context("spawn")
+    q = ctx.Queue()
+    port = _free_port()
+    procs = [ctx.Process(target=_planes_worker, args=(r, 2, port, shape, q)) for r in range(2)]
+    for p in procs:
+        p.start()
+    got = dict(q.get(timeout=120) for _ in procs)
+    for p in procs:
+        p.join(timeout=60)
+        assert p.exitcode == 0
+    want = np.arange(int(np.prod(shape)), dtype=np.int32).reshape(shape)
+    for rank in (0, 1):
+        assert np.array_equal(got[rank], want)
+
+
+def test_gather_planes_single_process_and_errors():
+    a = np.arange(24, dtype=np.int32).reshape(4, 6)
+    assert np.array_equal(D.gather_planes(a, (0, 4), (4, 6)), a)
+    with pytest.raises(ValueError):
+        D.gather_planes(a[:2], (0, 3), (4, 6))
+    with pytest.raises(ValueError):
+        D.gather_planes(a[:2].copy(), (0, 2), (4, 6))

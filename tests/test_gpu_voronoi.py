@@ -10,6 +10,22 @@ from oracle import voronoi_np
 pytestmark = pytest.mark.gpu
 
 
+def _oracle_chunk(args):
+    pts, vox, box = args
+    return voronoi_np.label_voxels(pts, 0, vox, box=box, chunk=128)
+
+
+def _label_voxels_parallel(pts, vox, box):
+    """The numpy oracle over a voxel list, one chunk per host core (2^18 voxels x 27 x 4096 image points)."""
+    import multiprocessing as mp
+    import os
+
+    cores = max(1, min(len(os.sched_getaffinity(0)), 32))
+    parts = np.array_split(vox, cores * 4)
+    with mp.get_context("spawn").Pool(cores) as pool:
+        return np.concatenate(pool.map(_oracle_chunk, [(pts, p, box) for p in parts]))
+
+
 @pytest.mark.parametrize("name", golden_names("vor"))
 def test_labels_match_reference_golden(sbx_lib, name):
     from simubox_b200 import VoronoiCell
@@ -93,7 +109,7 @@ def test_sparse_blob_masks(sbx_lib, shape, weights, periodic):
 
 def test_baseline_config_256_cubed_4096_seeds(sbx_lib):
     """BASELINE config 3: 256^3, 4096 jittered-lattice seeds, periodic, masked.  The reference loop
-    needs ~13 min there, so parity is on 2^14 random voxels + the 16^3 corner block (wrap-around),
+    needs ~13 min there, so parity is on 2^18 random voxels + the 16^3 corner block (wrap-around),
     plus whole-grid invariants."""
     import torch
     from simubox_b200 import VoronoiCell, synth
@@ -107,9 +123,9 @@ def test_baseline_config_256_cubed_4096_seeds(sbx_lib):
     lab, full, m = lab_t.cpu().numpy(), full_t.cpu().numpy(), mask.cpu().numpy()
     assert (lab[m == 0] == -1).all() and np.array_equal(lab[m != 0], full[m != 0])
     rng = np.random.default_rng(99)
-    vox = np.concatenate([rng.integers(0, 256, (1 << 14, 3)),
+    vox = np.concatenate([rng.integers(0, 256, (1 << 18, 3)),
                           np.stack(np.meshgrid(*[np.arange(16)] * 3, indexing="ij"), -1).reshape(-1, 3)])
-    ref = voronoi_np.label_voxels(pts, 0, vox, box=box, chunk=256)
+    ref = _label_voxels_parallel(pts, vox, box)
     assert np.array_equal(full[vox[:, 0], vox[:, 1], vox[:, 2]], ref)
     # every seed owns its own rounded position's neighbourhood; all 4096 labels appear
     assert len(np.unique(full)) == 4096
@@ -138,3 +154,78 @@ def test_one_shot_c_entry_point(sbx_lib):
                                                   C.c_void_p(lab.data_ptr()), None, st.ctypes.data_as(C.POINTER(C.c_int64))))
     ref = voronoi_np.label_grid(pts, 0, shape, box=tuple(float(n) for n in shape))
     assert np.array_equal(lab.cpu().numpy(), ref) and st[1] > 0
+
+
+@pytest.mark.parametrize("name", golden_names("vor"))
+def test_plane_ranges_match_reference_golden(sbx_lib, name):
+    """Voxel-slab decomposition: the grid labelled in plane ranges -- aligned and ragged cuts,
+    the way P = 2 / 3 ranks would own them -- equals the reference labels bit for bit.  Unweighted additive goldens
+    run the cell-list path here, weighted / power ones the tile path through its scratch grid."""
+    from simubox_b200 import VoronoiCell
+    from simubox_b200.distributed import shard_range
+
+    g = golden(name)
+    w = g["weights"] if g["weights"].ndim else float(g["weights"])
+    box = tuple(g["box"]) if g["box"].size else None
+    shape = tuple(int(n) for n in g["size"])
+    for world in (2, 3):
+        if shape[0] < world:
+            continue
+        parts = [VoronoiCell.label_grid(g["points"], w, shape=shape, method=str(g["method"]), box=box,
+                                        planes=shard_range(shape[0], r, world)) for r in range(world)]
+        assert np.array_equal(np.concatenate(parts, axis=0), g["labels"]), f"world {world}"
+
+
+@pytest.mark.parametrize("shape,S,periodic,masked", [
+    ((64, 48, 40), 150, True, True), ((37, 29, 23), 40, True, False), ((33, 20, 27), 60, False, True), ((48, 48, 48), 1, True, False),
+    ((16, 16, 16), 900, True, False), ((70, 90), 25, True, True), ((128, 96), 300, False, False), ((9, 5, 3), 3, True, False)])
+def test_cell_path_ranges_match_oracle(sbx_lib, shape, S, periodic, masked):
+    """The cell-list path on random seeds (seeds outside the box, dense and single-seed cases, 2D and 3D, ragged
+    grids), labelled in P = 1 (forced range), 2, 4 and 8 plane ranges on one device, against the numpy oracle."""
+    from simubox_b200 import VoronoiCell
+    from simubox_b200.distributed import shard_range
+
+    rng = np.random.default_rng(S + sum(shape))
+    pts = rng.uniform(-0.1, 1.1, (S, len(shape))) * np.array(shape)
+    box = tuple(float(n) for n in shape) if periodic else None
+    mask = (rng.random(shape) > 0.5) if masked else None
+    ref = voronoi_np.label_grid(pts, 0, shape, box=box, mask=mask)
+    for world in (2, 4, 8):
+        spans = [shard_range(shape[0], r, world) for r in range(world)]
+        parts = [VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, planes=sp) for sp in spans if sp[1] > sp[0]]
+        assert np.array_equal(np.concatenate(parts, axis=0), ref), f"world {world}"
+    lab, st = VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, planes=(0, shape[0] - 1), stats=True)
+    assert np.array_equal(lab, ref[:-1]) and st["tiles"] > 0
+
+
+def test_cell_path_exact_ties_and_clusters(sbx_lib):
+    """Lattice seeds (every cell face is an exact tie: the fp32 pre-decision must hand those voxels to the fp64
+    fallback) and clustered duplicates (more candidates than the staging buffer: box-scan path), in plane ranges."""
+    from simubox_b200 import VoronoiCell
+
+    shape = (32, 32, 32)
+    ax = np.arange(4) * 8.0 + 4.0
+    lattice = np.stack(np.meshgrid(ax, ax, ax, indexing="ij"), -1).reshape(-1, 3)
+    for pts, box in ((lattice, (32.0, 32.0, 32.0)), (lattice[::-1].copy(), None)):
+        ref = voronoi_np.label_grid(pts, 0, shape, box=box)
+        got = np.concatenate([VoronoiCell.label_grid(pts, 0, shape=shape, box=box, planes=(a, a + 8)) for a in range(0, 32, 8)], axis=0)
+        assert np.array_equal(got, ref)
+    rng = np.random.default_rng(11)
+    pts = np.concatenate([np.tile([[8.0, 8.0, 8.0]], (100, 1)), rng.uniform(7.9, 8.1, (100, 3)), rng.uniform(0, 16, (20, 3))])
+    ref = voronoi_np.label_grid(pts, 0, (16, 16, 16))
+    lab, st = VoronoiCell.label_grid(pts, 0, shape=(16, 16, 16), planes=(0, 15), stats=True)
+    assert st["overflow_tiles"] > 0 and np.array_equal(lab, ref[:15])
+
+
+def test_cell_path_256_cubed_slabs_equal_whole_grid(sbx_lib):
+    """BASELINE config 3 labelled as 8 slabs of 32 planes (cell path) = the single-launch labelling (tile path)."""
+    import torch
+    from simubox_b200 import VoronoiCell, synth
+
+    shape, box = (256, 256, 256), (256.0, 256.0, 256.0)
+    pts = synth.seeds_lattice(shape, 16, 4.0, 1234)
+    mask = (synth.fields_torch(1, 1, shape, cells=4)[0] > 0.5).to(torch.uint8)
+    whole = VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, return_tensor=True)
+    for lo in range(0, 256, 32):
+        part = VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, return_tensor=True, planes=(lo, lo + 32))
+        assert torch.equal(part, whole[lo:lo + 32])
