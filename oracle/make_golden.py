@@ -115,6 +115,60 @@ def gen_scatter():
                          store_input=(n <= 32), extra=dict(field_index=idx, cells=2, checksum=float(mat.sum())))
 
 
+def gen_scatter_baseline():
+    """BASELINE.json configs 2 and 4 at their full grid sizes through the LIVE reference: 128^3 fields 0-7 (cells = 2,
+    SURVEY.md 8(d) config 2 'parity subset') and two 256^3 fields (cells = 4).  Inputs are regenerated in the tests
+    from the closed-form generator (checksum stored); a 256^3 reference run needs ~5 GB and ~15 s."""
+    pk2 = dict(width=0.5, step=2000, cutoff=20, min_height=1)
+    for n, cells, fields in ((128, 2, range(8)), (256, 4, range(2))):
+        for idx in fields:
+            mat = synth.field_numpy(idx, (n, n, n), cells=cells)
+            scatter_case(f"scatter_synth_{n}_f{idx}", mat, synth.box_for(cells), cutoff=30, peak_kw=pk2, store_input=False,
+                         extra=dict(field_index=idx, cells=cells, checksum=float(mat.sum())))
+
+
+def demo_density(sb_or_mod, mat, NxNyNz, lxlylz):
+    """A ``Density`` holding one column, the way ``read_density`` builds it (reader.py:218-230)."""
+    import pandas as pd
+
+    N = np.asarray(NxNyNz)
+    return sb_or_mod.Density(path=None, data=pd.DataFrame(np.asarray(mat).reshape(-1, 1)), NxNyNz=N, lxlylz=np.asarray(lxlylz, dtype=np.float64)[N != 1],
+                             shape=N[N != 1])
+
+
+def gen_analyze():
+    """``VoronoiCell.OpenCV`` / ``Analyze`` (VORONOI and TRIANGLE modes) of the live reference on the notebook's own
+    example (demos/scripts.ipynb cell 28: demos/datasets/voronoi, slices=(0, 0), expand=3): 67 centres, Qhull
+    vertices and ridges, filtered Delaunay triangles, coord_dict.  The input field is the one already stored in
+    scatter_voronoi_demo_2x64x128.npz."""
+    sb = ref_live.load()
+    d = sb.toolkit.read_density(REF / "demos/datasets/voronoi/phout.txt")
+    d.repair_from_printout(sb.toolkit.read_printout(REF / "demos/datasets/voronoi/printout.txt"))
+    stored = np.load(OUT / "scatter_voronoi_demo_2x64x128.npz")
+    assert np.array_equal(stored["mat"], d.data[0].values.reshape(d.shape)) and np.array_equal(stored["L"], d.lxlylz)
+    with warnings.catch_warnings():
+        warnings.simplefilter("ignore")
+        tri = sb.calculator.VoronoiCell.Analyze(d, sb.schema.AnalyzeMode.TRIANGLE, slices=(0, 0), expand=3, interactive=False)
+        tri60 = sb.calculator.VoronoiCell.Analyze(d, sb.schema.AnalyzeMode.TRIANGLE, slices=(0, 0), expand=3, interactive=False, theta_max=np.pi / 3 * 1.2)
+        vor = sb.calculator.VoronoiCell.Analyze(d, sb.schema.AnalyzeMode.VORONOI, slices=(0, 0), expand=3, interactive=False)
+    cv = tri.cv_result
+    pd_ = cv.parsed_density
+    vecs = [np.linspace(0, l, N) for l, N in zip(pd_.lxlylz, pd_.NxNyNz)][::-1]
+    X, Y = np.meshgrid(*vecs)
+    c = np.around(cv.centers).astype(int)
+    centers_lxly = np.stack([X[c[:, 1], c[:, 0]], Y[c[:, 1], c[:, 0]]], axis=1)
+    assert np.array_equal(vor.voronoi.points, centers_lxly)
+    keys = sorted(int(k) for k in tri.coord_dict)
+    pairs = np.array([(k, int(v)) for k in keys for v in sorted(tri.coord_dict[k])], dtype=np.int32)
+    np.savez_compressed(OUT / "analyze_voronoi_demo.npz", centers=cv.centers, centers_lxly=centers_lxly, tiled=pd_.mat.squeeze(),
+                        tiled_lxlylz=pd_.lxlylz, triangles=np.array(tri.triangle, dtype=np.int32), coord_pairs=pairs,
+                        triangles_theta72=np.array(tri60.triangle, dtype=np.int32),
+                        vor_vertices=vor.voronoi.vertices, vor_ridge_points=vor.voronoi.ridge_points.astype(np.int32),
+                        point_cut=sb.calculator.VoronoiCell.set_point_limits(cv, centers_lxly))
+    print(f"  analyze_voronoi_demo: {len(cv.centers)} centres, {len(tri.triangle)} triangles ({len(tri60.triangle)} at 72 deg), "
+          f"{len(vor.voronoi.vertices)} Voronoi vertices")
+
+
 def gen_voronoi():
     rng = np.random.default_rng(77)
     cases = []
@@ -252,7 +306,16 @@ def main():
         numpy=np.__version__, scipy=scipy.__version__, pandas=pandas.__version__, cv2=cv2.__version__,
         pydantic=pydantic.__version__, python=sys.version.split()[0],
         pinned_by_reference=dict(numpy="1.26.4", scipy="1.11.4", pandas="2.1.4", opencv="4.8.1.78")), indent=1))
+    only = set(sys.argv[1:])
+    if only:  # e.g. python -m oracle.make_golden baseline analyze  (adds fixtures without rewriting the others)
+        if "baseline" in only:
+            print("scatter, BASELINE grid sizes:"); gen_scatter_baseline()
+        if "analyze" in only:
+            print("analyze:"); gen_analyze()
+        return
     print("scatter:"); gen_scatter()
+    print("scatter, BASELINE grid sizes:"); gen_scatter_baseline()
+    print("analyze:"); gen_analyze()
     print("voronoi:"); gen_voronoi()
     print("reader:"); gen_reader()
     print("splat:"); gen_splat()

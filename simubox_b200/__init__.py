@@ -5,16 +5,17 @@ Drop-in for the corresponding SimuBox entry points (same names and signatures):
 ``Density`` / ``ScatterResult`` / ``ScatterPlot`` models.  All numerics run in
 ``libsimubox_b200.so`` (hand-written sm_100a CUDA + cuFFT); there is no CPU fallback.
 """
-from .schema import (AnalyzeMode, ColorMode, Density, DensityParseResult, OpenCVResult, Printout,
-                     ScatterPlot, ScatterResult, WeightedMode, XML, XMLTransResult)
-from .reader import check_filepath, parse_density, read_density, read_printout
+from .schema import (AnalyzeMode, ColorMode, Density, DensityParseResult, Fet, OpenCVResult, Printout,
+                     ScatterPlot, ScatterResult, VoronoiAnalyzeResult, WeightedMode, XML, XMLTransResult)
+from .reader import check_filepath, parse_density, read_density, read_fet, read_printout
 from .peak import gaussian_expansion
 from .scatter import Scatter
 from .voronoi import VoronoiCell
 from .xmltrans import XmlTransformer, splat_particles
 
 __all__ = [
-    "AnalyzeMode", "ColorMode", "Density", "DensityParseResult", "OpenCVResult", "Printout", "ScatterPlot",
-    "ScatterResult", "WeightedMode", "check_filepath", "parse_density", "read_density", "read_printout",
+    "AnalyzeMode", "ColorMode", "Density", "DensityParseResult", "Fet", "OpenCVResult", "Printout", "ScatterPlot",
+    "ScatterResult", "VoronoiAnalyzeResult", "WeightedMode", "check_filepath", "parse_density", "read_density", "read_fet",
+    "read_printout",
     "gaussian_expansion", "Scatter", "VoronoiCell", "XML", "XMLTransResult", "XmlTransformer", "splat_particles",
 ]

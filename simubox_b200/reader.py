@@ -21,7 +21,7 @@ from typing import Iterable, Optional, Sequence, Union
 import numpy as np
 import pandas as pd
 
-from .schema import Density, DensityParseResult, FileLike, PathLike, Printout, RealNum
+from .schema import Density, DensityParseResult, Fet, FileLike, PathLike, Printout, RealNum
 
 
 def check_filepath(path: PathLike, filename: str) -> Path:
@@ -48,6 +48,22 @@ def read_printout(path: PathLike, filename: str = "printout.txt", mode: str = "r
         freeS=summary[4], freeWS=summary[3] + summary[4], inCompMax=summary[-1],
         volumes=floats(lines[-5], 2), potentials=floats(lines[-4], 2),
     )
+
+
+def read_fet(path: FileLike, filename: str = "fet.dat", mode: str = "r", encoding: str = "utf-8", **kwargs) -> Fet:
+    """SCFT ``fet.dat``: one ``<index> <key> <value>`` triple per non-blank line -> :class:`Fet`
+    (reference reader.py:289-313; feeds ``Density.repair_from_fet``, web/pages/2_Scatter.py:95).
+
+    The reference's own body unpacks ``readlines()`` into two names (reader.py:306) and therefore raises
+    ``ValueError`` on any file that does not have exactly two lines [probed]; this is the parse its next three
+    lines spell out: drop the first token, ``key, value = rest``, ``float(value)``."""
+    path = check_filepath(path, filename=filename)
+    with path.open(mode=mode, encoding=encoding) as fh:
+        rows = [line.strip().split()[1:] for line in fh if line.strip()]
+    res = {}
+    for key, val in rows:  # a line with another token count raises ValueError, as the reference's loop would
+        res[key] = float(val)
+    return Fet(path=path, **res)
 
 
 def _bad_grid(vec: np.ndarray) -> bool:

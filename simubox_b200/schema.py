@@ -69,6 +69,43 @@ class Printout(MixinBaseModel):
     potentials: Optional[np.ndarray] = None
 
 
+class Fet(MixinBaseModel):
+    """SCFT ``fet.dat`` key/value file (reference DataFile.py:38-74): every field optional, unknown keys ignored
+    (pydantic's default, as in the reference)."""
+    path: Optional[Path] = None
+    xACN: Optional[float] = None
+    xCAN: Optional[float] = None
+    xABN: Optional[float] = None
+    xBAN: Optional[float] = None
+    xCBN: Optional[float] = None
+    xBCN: Optional[float] = None
+    stressX: Optional[float] = None
+    stressY: Optional[float] = None
+    stressZ: Optional[float] = None
+    lx: Optional[float] = None
+    ly: Optional[float] = None
+    lz: Optional[float] = None
+    lx_full: Optional[float] = None
+    ly_full: Optional[float] = None
+    lz_full: Optional[float] = None
+    freeEnergy: Optional[float] = None
+    freeAB_sum: Optional[float] = None
+    freeAB: Optional[float] = None
+    freeBA: Optional[float] = None
+    freeAC: Optional[float] = None
+    freeCA: Optional[float] = None
+    freeBC: Optional[float] = None
+    freeCB: Optional[float] = None
+    freeW: Optional[float] = None
+    freeS: Optional[float] = None
+    freeDiff: Optional[float] = None
+    inCompMax: Optional[float] = None
+    Q0: Optional[float] = None
+    VolumeFraction0: Optional[float] = None
+    sumVolume: Optional[float] = None
+    activity0: Optional[float] = None
+
+
 class Density(MixinBaseModel):
     """Parsed phout/phin/block file (reference DataFile.py:77-86)."""
     path: Optional[Path] = None
@@ -127,6 +164,16 @@ class OpenCVResult(MixinBaseModel):
     parsed_density: DensityParseResult
     facets: Sequence
     centers: np.ndarray
+
+
+class VoronoiAnalyzeResult(FigureAxesMixin):
+    """Reference ComputedRes.py:51-56.  ``voronoi`` is the ``scipy.spatial.Voronoi`` object, ``triangle`` the list of
+    kept Delaunay simplices, ``coord_dict`` centre -> set of neighbouring centres."""
+    path: Optional[Path] = None
+    cv_result: OpenCVResult
+    voronoi: Optional[Any] = None
+    triangle: Optional[list] = None
+    coord_dict: Optional[dict] = None
 
 
 class XML(MixinBaseModel):

@@ -5,8 +5,10 @@ entry points (SimuBox/calculator/voronoi.py:29-327).
 ``label_grid`` is the addition that returns what the reference only paints: the int32 label
 array, computed by ``sbx_voronoi_label`` (2D or 3D, optional periodic box and uint8 mask).
 ``weighted_voronoi_diagrams`` keeps its signature and routes the per-pixel loop
-(voronoi.py:284-292) through ``label_grid``.  ``OpenCV`` (the 2D seed finder) stays on the CPU
-with cv2, as in the reference.
+(voronoi.py:284-292) through ``label_grid``.  ``OpenCV`` (the 2D seed finder) and ``Analyze`` with its ``voronoi`` /
+``triangle`` modes (voronoi.py:70-241: centres -> box coordinates, Qhull Voronoi, angle-filtered Delaunay,
+``coord_dict``) stay on the CPU with cv2 / scipy as in the reference -- 67 centres, milliseconds; their figures are
+drawn only when matplotlib is importable (no graphics stack on this box), the numeric results always.
 """
 from __future__ import annotations
 
@@ -18,7 +20,7 @@ import numpy as np
 from . import _lib
 from ._device import ptr, stream_ptr, to_device, torch_cuda
 from .reader import parse_density
-from .schema import ColorMode, Density, OpenCVResult, WeightedMode
+from .schema import AnalyzeMode, ColorMode, Density, OpenCVResult, VoronoiAnalyzeResult, WeightedMode
 
 _MODES = {"additive": 0, "power": 1}
 _PLANS: dict = {}
@@ -255,6 +257,128 @@ class VoronoiCell:
         if interactive:
             plt.show()
         return fig, ax
+
+    # ------------------------------------------------------------------ Analyze (reference voronoi.py:70-241)
+    @staticmethod
+    def in_lim(point, xlim, ylim):
+        """Points strictly inside the window (reference voronoi.py:70-77)."""
+        return (xlim[0] < point[:, 0]) & (point[:, 0] < xlim[1]) & (ylim[0] < point[:, 1]) & (point[:, 1] < ylim[1])
+
+    @staticmethod
+    def get_lim_attributes(key: str, default: Sequence, expand, **kwargs):
+        """Window in units of the raw box, shifted by half the expansion (reference voronoi.py:103-106)."""
+        return np.array(kwargs.get(key, default)) + expand / 2
+
+    @classmethod
+    def set_point_limits(cls, density: OpenCVResult, centers: np.ndarray, **kwargs):
+        """Centres inside the plotted window (reference voronoi.py:215-230)."""
+        pd_ = density.parsed_density
+        xlim = cls.get_lim_attributes("point_xlim", (-0.1, 1.1), pd_.expand[0], **kwargs)
+        ylim = cls.get_lim_attributes("point_ylim", (-0.1, 1.1), pd_.expand[1], **kwargs)
+        return centers[cls.in_lim(point=centers, xlim=pd_.raw_lxlylz[1] * xlim, ylim=pd_.raw_lxlylz[0] * ylim)]
+
+    @classmethod
+    def set_axis_limits(cls, density: OpenCVResult, **kwargs):
+        """Axis window of the figure (reference voronoi.py:232-241); returns (xlim, ylim) and applies them when a
+        matplotlib figure is current."""
+        pd_ = density.parsed_density
+        xlim = pd_.raw_lxlylz[1] * cls.get_lim_attributes("axis_xlim", (-0.5, 1.5), pd_.expand[0], **kwargs)
+        ylim = pd_.raw_lxlylz[0] * cls.get_lim_attributes("axis_ylim", (-0.5, 1.5), pd_.expand[1], **kwargs)
+        try:
+            import matplotlib.pyplot as plt
+
+            plt.xlim(xlim)
+            plt.ylim(ylim)
+        except Exception:
+            pass
+        return xlim, ylim
+
+    @classmethod
+    def Analyze(cls, density: Density, mode: AnalyzeMode, **kwargs) -> VoronoiAnalyzeResult:
+        """Domain centres of the tiled field -> box coordinates -> Voronoi diagram or filtered Delaunay
+        triangulation (reference voronoi.py:79-101).  ``kwargs`` go to ``OpenCV`` / ``parse_density`` and to the
+        mode function exactly as in the reference (``expand`` is consumed by ``OpenCV``)."""
+        cv_res = cls.OpenCV(density, **kwargs)
+        kwargs.pop("expand", None)
+        pd_ = cv_res.parsed_density
+        vecs = [np.linspace(0, l, N) for l, N in zip(pd_.lxlylz, pd_.NxNyNz)][::-1]
+        X, Y = np.meshgrid(*vecs)
+        centers = np.around(cv_res.centers).astype(int)
+        centers_lxly = np.stack([X[centers[:, 1], centers[:, 0]], Y[centers[:, 1], centers[:, 0]]], axis=1)
+        if mode == AnalyzeMode.VORONOI:
+            return cls.voronoi(cv_res, centers_lxly, **kwargs)
+        if mode == AnalyzeMode.TRIANGLE:
+            return cls.triangle(cv_res, centers_lxly, **kwargs)
+        raise NotImplementedError(f"analysis mode {mode} is not implemented")
+
+    @classmethod
+    def voronoi(cls, cv_res: OpenCVResult, centers: np.ndarray, interactive: bool = True, save=False, **kwargs) -> VoronoiAnalyzeResult:
+        """``scipy.spatial.Voronoi(centers, incremental=True)`` (Qhull; reference voronoi.py:108-148).  The figure
+        (``voronoi_plot_2d`` + the centres inside the point window) is drawn when matplotlib is importable."""
+        from scipy.spatial import Voronoi
+
+        centers_cut = cls.set_point_limits(cv_res, centers, **kwargs)
+        vor = Voronoi(centers, incremental=True)
+        fig = ax = None
+        try:
+            import matplotlib.pyplot as plt
+            from scipy.spatial import voronoi_plot_2d
+
+            asp = cv_res.parsed_density.lxlylz[1] / cv_res.parsed_density.lxlylz[0]
+            plt.figure()
+            ax = plt.gca()
+            fig = voronoi_plot_2d(vor, ax, show_points=False, show_vertices=False, line_colors=kwargs.get("lc", "k"))
+            if kwargs.get("point", True):
+                plt.scatter(centers_cut[:, 0], centers_cut[:, 1], s=20, c=kwargs.get("pc", "b"))
+            cls.set_axis_limits(cv_res, **kwargs)
+            ax.set_aspect(1 / asp)
+            if interactive:
+                plt.show()
+        except Exception:
+            fig = ax = None
+        return VoronoiAnalyzeResult(path=cv_res.path, cv_result=cv_res, fig=fig, ax=ax, voronoi=vor)
+
+    @classmethod
+    def triangle(cls, cv_res: OpenCVResult, centers: np.ndarray, interactive: bool = True, save=False, **kwargs) -> VoronoiAnalyzeResult:
+        """Delaunay triangles of the centres without those whose largest angle exceeds ``theta_max`` (default
+        pi / 2), and the neighbour sets they induce (reference voronoi.py:150-213).  Arithmetic as there: edge
+        lengths from ``cdist``, ``a <= b <= c`` sorted, ``acos((a^2 + b^2 - c^2) / (2ab))``."""
+        from collections import defaultdict
+        from math import acos
+
+        from scipy.spatial import Delaunay, distance
+
+        centers_cut = cls.set_point_limits(cv_res, centers, **kwargs)
+        theta_max = kwargs.get("theta_max", np.pi / 2)
+        dist_matrix = distance.cdist(centers, centers, "euclidean")
+        triangles = []
+        for t in Delaunay(centers).simplices:
+            a, b, c = sorted([dist_matrix[t[0], t[1]], dist_matrix[t[0], t[2]], dist_matrix[t[1], t[2]]])
+            if acos((a ** 2 + b ** 2 - c ** 2) / (2 * a * b)) > theta_max:
+                continue
+            triangles.append(t)
+        coord_dict = defaultdict(set)
+        for t in triangles:
+            coord_dict[t[0]].update([t[1], t[2]])
+            coord_dict[t[1]].update([t[0], t[2]])
+            coord_dict[t[2]].update([t[0], t[1]])
+        fig = ax = None
+        try:
+            import matplotlib.pyplot as plt
+
+            asp = cv_res.parsed_density.lxlylz[1] / cv_res.parsed_density.lxlylz[0]
+            fig = plt.figure(figsize=kwargs.get("figsize", (6, 6 / asp)))
+            ax = plt.gca()
+            plt.triplot(centers[:, 0], centers[:, 1], triangles, linewidth=1, color=kwargs.get("lc", "k"))
+            if kwargs.get("point", True):
+                plt.scatter(centers_cut[:, 0], centers_cut[:, 1], s=20, c=kwargs.get("pc", "b"))
+            cls.set_axis_limits(cv_res, **kwargs)
+            ax.set_aspect(asp)
+            if interactive:
+                plt.show()
+        except Exception:
+            fig = ax = None
+        return VoronoiAnalyzeResult(path=cv_res.path, cv_result=cv_res, fig=fig, ax=ax, triangle=triangles, coord_dict=coord_dict)
 
     # ------------------------------------------------------------------ CPU seed finder (as the reference)
     @staticmethod

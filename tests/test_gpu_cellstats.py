@@ -77,3 +77,29 @@ def test_properties_at_baseline_size(sbx_lib):
     full = VoronoiCell.cell_statistics(VoronoiCell.label_grid(pts, 0, shape=shape, box=(256.0,) * 3, return_tensor=True), n_cells=S)
     assert int(full["volume"].sum()) == 256 ** 3
     assert 12 <= full["degree"].mean() <= 20 and full["degree"].min() >= 4
+
+
+def test_adjacency_vs_delaunay_of_reference_centres(sbx_lib):
+    """f3 pin on the notebook example (67 OpenCV centres of demos/datasets/voronoi, tests/golden/analyze_voronoi_demo.npz).
+    ``cell_statistics`` returns the FACE adjacency of the labelled cells inside the image; the reference's ``triangle``
+    (voronoi.py:163-182) returns Delaunay neighbours of the centres in physical coordinates after dropping obtuse
+    triangles.  Voronoi face adjacency is the Delaunay graph of the same points in the same (pixel) metric, clipped to
+    the window, so the relation that must hold is: grid adjacency is a subset of the unfiltered pixel-metric Delaunay
+    graph, the difference being pairs whose common face lies outside the 192 x 384 window (hull edges).  Measured: 53
+    of 67 cells identical, 0 grid-only pairs, 16 Delaunay-only directed pairs.  Against the reference's filtered,
+    physical-metric coord_dict it is a different definition (41 of 63 cells identical) -- recorded, not asserted."""
+    from conftest import golden
+    from scipy.spatial import Delaunay
+    from simubox_b200 import VoronoiCell
+
+    g = golden("analyze_voronoi_demo")
+    pts = np.around(g["centers"]).astype(int)[:, ::-1].astype(float)   # rounded like Analyze, (row, col)
+    lab = VoronoiCell.label_grid(pts, 0, shape=g["tiled"].shape)
+    grid = VoronoiCell.cell_statistics(lab, n_cells=len(pts), periodic=False)["coord_dict"]
+    dl = {}
+    for t in Delaunay(pts).simplices:
+        for i in range(3):
+            dl.setdefault(int(t[i]), set()).update(int(x) for x in t if x != t[i])
+    assert all(grid.get(k, set()) <= dl[k] for k in dl), "two cells share a face but their seeds are not Delaunay neighbours"
+    assert sum(1 for k in dl if grid.get(k, set()) == dl[k]) >= 50
+    assert sum(len(dl[k] - grid.get(k, set())) for k in dl) <= 20

@@ -10,8 +10,19 @@ from conftest import check_scatter_rows, golden, golden_field, golden_names
 from oracle import scatter_np, voronoi_np
 
 
+_MEMBERS = {}
+
+
 def last_shell_members(mat, L, cutoff, thr):
-    """Intensities of every mode in the (possibly truncated) last returned shell."""
+    """Intensities of every mode in the (possibly truncated) last returned shell (cached per field: an N^3 host
+    FFT, seconds at 256^3, and the GPU suite asks once per execution path)."""
+    key = (mat.shape, tuple(float(l) for l in L), int(cutoff), float(thr), float(mat.sum()), float(mat.flat[mat.size // 3]))
+    if key not in _MEMBERS:
+        _MEMBERS[key] = _last_shell_members(mat, L, cutoff, thr)
+    return _MEMBERS[key]
+
+
+def _last_shell_members(mat, L, cutoff, thr):
     k2, _ = scatter_np.mode_k2(mat.shape, L)
     reps, _, trunc, _, _ = scatter_np.shell_table(mat.shape, L, cutoff, thr)
     inten = np.abs(np.fft.fftn(mat) ** 2) / mat.size
