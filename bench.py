@@ -7,8 +7,14 @@ gyroid/BCC 128^3 fp64 fields, BASELINE.json config 2).  ``value`` = device-resid
 fields/s; ``e2e`` = the same through the host-buffer C-ABI call (pinned host -> device copies
 inside the timed region); ``roofline`` = the dominant hand-written kernel against the measured
 HBM peak; ``cpu_baseline`` = the numpy port of the reference on this host's cores.
-``--impl reference`` times that CPU port alone.  ``--workload voronoi`` reports voxels/s of the
-256^3 / 4096-seed periodic masked labelling (BASELINE.json config 3) instead.
+``--impl reference`` times that CPU port alone.
+
+The default line also carries the rest of BASELINE.json's metric as sub-records (each leg a few seconds):
+``"voronoi"`` (256^3 / 4096 seeds / uint8 mask, config 3: voxels/s, roofline, e2e, cpu_baseline, parity),
+``"sweep"`` (config 4 at its stated 256 fields of 256^3 per GPU: scatter + Voronoi per field) and, with
+``--gpus N > 1``, ``"slab"`` (config 5: one 1024^3 field through the real NCCL path in both modes, stage split,
+all-to-all GB/s, parity of the two modes) and ``"voronoi_sharded"`` (one 256^3 and one 512^3 grid by voxel slab,
+strong scaling).  ``--workload voronoi|slab|sweep`` prints one of those records alone; ``--sub none`` drops them.
 """
 from __future__ import annotations
 
@@ -153,18 +159,25 @@ def cpu_voronoi_baseline(pts, shape, box, voxels, cores):
 
 
 # ----------------------------------------------------------------------------- distributed plumbing
+_CTX = None
+
+
 def dist_setup(gpus):
+    """(rank, world, local) -- the process group is created once per process."""
+    global _CTX
     import torch
 
-    rank = int(os.environ.get("RANK", "0"))
-    world = int(os.environ.get("WORLD_SIZE", "1"))
-    local = int(os.environ.get("LOCAL_RANK", "0"))
-    if world > 1:
-        import torch.distributed as dist
+    if _CTX is None:
+        rank = int(os.environ.get("RANK", "0"))
+        world = int(os.environ.get("WORLD_SIZE", "1"))
+        local = int(os.environ.get("LOCAL_RANK", "0"))
+        if world > 1:
+            import torch.distributed as dist
 
-        torch.cuda.set_device(local)
-        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
-    return rank, world, local
+            torch.cuda.set_device(local)
+            dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        _CTX = (rank, world, local)
+    return _CTX
 
 
 def barrier(world):
@@ -244,16 +257,24 @@ def run_scatter(args):
         time.sleep(0.05)
     plan.set_profiling(False)
     ms = timed_steps(step_device, args.steps, args.warmup, world, dev)
-    # --- same steps again with per-stage CUDA events (transform vs hand-written kernel split)
+    # --- same steps again with per-stage CUDA events (transform vs hand-written kernel split): one profile per step,
+    # warm-up step dropped, MEDIAN over the steps (a sum over all launches once let a single perturbed step put the
+    # kernel time above the step time)
     plan.set_profiling(True)
     plan.profile(reset=True)
-    timed_steps(step_device, args.steps, 1, world, dev)
-    prof = plan.profile(reset=True)
+    per_step = []
+    for i in range(args.steps + 1):
+        step_device()
+        pr = plan.profile(reset=True)  # synchronises on the step's last event
+        if i:
+            per_step.append(pr)
+    barrier(world)
     plan.set_profiling(False)
-    own_per_step = prof["own_launches"] / (args.steps + 1)
-    fused_ms_per_launch = prof["fused_ms"] / max(prof["own_launches"], 1)
-    transform_ms_per_step = prof["transform_ms"] / (args.steps + 1)
-    fused_ms_per_step = prof["fused_ms"] / (args.steps + 1)
+    med = lambda key: float(np.median([pr[key] for pr in per_step]))
+    own_per_step = med("own_launches")
+    transform_ms_per_step, fused_ms_per_step = med("transform_ms"), med("fused_ms")
+    fused_ms_per_launch = fused_ms_per_step / max(own_per_step, 1)
+    prof = {"transform_ms": transform_ms_per_step, "fused_ms": fused_ms_per_step, "own_launches": own_per_step}
 
     # --- end to end through the host-buffer C-ABI call (pinned host memory)
     host = torch.empty((B, *shape), dtype=torch.float64, pin_memory=True)
@@ -280,8 +301,13 @@ def run_scatter(args):
     d2h = B * (ns * 8 + 4 + 256 * 4)
     assert np.array_equal(last["host"]["I"], last["out"]["I"].cpu().numpy()) or plan.path == 1, "host and device paths disagree"
 
+    del host, fields
+    last_out = {k: (v.cpu() if hasattr(v, "cpu") else v) for k, v in last["out"].items()}
+    last.clear()
+    torch.cuda.empty_cache()
     if rank != 0:
-        return
+        return None
+    last["out"] = last_out
     peak, peak_src = measured_peak_gbs()
     spec_bytes = 16 * n * n * (n // 2 + 1)
     pipeline_bytes = 8 * n ** 3 + 2 * spec_bytes
@@ -290,6 +316,10 @@ def run_scatter(args):
         kern, unit_bytes = (plan.kernel or "pruned_fused_kernel"), 8 * n ** 3
         launches_per_step = own_per_step
         fused_ms_per_launch = prof["transform_ms"] / max(prof["own_launches"], 1)
+        if fused_ms_per_launch * launches_per_step > ms:
+            # the kernel IS the step here (one launch per step); event pairs of the profiled pass cannot undercut the
+            # un-profiled step they repeat, so a larger median means the profiled pass was perturbed: use the step time
+            fused_ms_per_launch = ms / max(launches_per_step, 1)
     elif plan.path == 3:  # pruned DFT: pruned_planes_kernel reads each field exactly once (first event pair)
         kern, unit_bytes = "pruned_planes_kernel", 8 * n ** 3
         launches_per_step = own_per_step / 2
@@ -335,12 +365,13 @@ def run_scatter(args):
                 "ms_per_step": e2e_ms, "h2d_GBps": h2d / (e2e_ms * 1e-3) / 1e9, "api": "Scatter.sacttering_peak_batch(pinned host tensor) -> sbx_scatter_execute_host"},
         "gpu_launches": int(round(own_per_step * args.steps)),
         "roofline": roof,
-        "cpu_baseline": {"value": cpu_rate, "unit": "fields/s", "cores": cores, "kind": "port",
-                         "sample": f"{sample} fields of the same generator through oracle/scatter_np.scattering_peak + show_peak, one field per worker process"},
+        "cpu_baseline": {"value": cpu_rate, "unit": "fields/s", "cores": cores, "kind": "port", "txyz": "vectorised",
+                         "sample": f"{sample} fields of the same generator through oracle/scatter_np.scattering_peak + show_peak, one field per worker process",
+                         "note": "per-field rate of a bounded sample; the port builds txyz vectorised, ~3.6x faster per core than the reference's itertools.product (SURVEY.md 6), so GPU/CPU ratios are conservative"},
         "parity_vs_cpu_sample": parity,
         "clocks": clocks,
     }
-    print(json.dumps(out))
+    return out
 
 
 # ----------------------------------------------------------------------------- voronoi workload
@@ -409,8 +440,10 @@ def run_voronoi(args):
     for _ in range(args.e2e_steps):
         step_host()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.e2e_steps, world, dev)
+    del flush
+    torch.cuda.empty_cache()
     if rank != 0:
-        return
+        return None
     peak, peak_src = measured_peak_gbs()
     S = per_axis ** 3
     vox = n ** 3
@@ -433,34 +466,29 @@ def run_voronoi(args):
                      "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(f"coarse_kernel+mid_kernel+label_kernel|{n}^3|{S} seeds"),
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_grid": unit_bytes, "evaluations_per_live_voxel": st["evaluations"] / max(live, 1),
-                     "overflow_tiles": st["overflow_tiles"]},
+                     "overflow_tiles": st["overflow_tiles"],
+                     "note": "issue/latency bound, not HBM bound (DESIGN.md section 4): three launches, fp64 argmin over ~3.3 candidates per voxel"},
         "cpu_baseline": {"value": cpu_rate, "unit": "voxels/s", "cores": cores, "kind": "port",
                          "sample": f"{args.cpu_voxels} random voxels of the same grid through oracle/voronoi_np.label_voxels (27 images x {S} seeds per voxel)"},
         "parity_vs_cpu_sample": parity, "clocks": clocks,
     }
-    print(json.dumps(out))
+    return out
 
 
 # ----------------------------------------------------------------------------- one giant field, slab decomposed
-def run_slab(args):
-    """BASELINE config 5: ONE --grid^3 fp64 field, N0/world planes per rank, cuFFT 2D -> NCCL all-to-all ->
-    cuFFT 1D -> fused histogram -> all-reduce.  Strong scaling: the field is fixed, ranks split it."""
+def _slab_mode(args, mode, local_slab, ctx):
+    """One mode of the slab-decomposed scatter ('pruned' or 'fft') on this rank's planes: ms per step (CUDA events, max
+    over ranks), stage split averaged over >= 10 profiled steps each started at a barrier, the rows."""
     import torch
 
     from simubox_b200 import distributed as D, synth
 
-    rank, world, local = dist_setup(args.gpus)
+    rank, world, local = ctx
     dev = torch.device("cuda", local)
-    torch.cuda.set_device(dev)
     n = args.grid
-    L = synth.box_for(args.cells)
-    slab = D.SlabScatter((n, n, n), L, cutoff=30, device=local)
-    lo, hi = slab.planes
-    # this rank's planes of the synthetic field, generated on the device plane block by plane block
-    local_slab = torch.empty((hi - lo, n, n), dtype=torch.float64, device=dev)
-    for x0 in range(lo, hi, 32):
-        x1 = min(hi, x0 + 32)
-        local_slab[x0 - lo:x1 - lo] = synth.field_planes_torch(3, (n, n, n), x0, x1, cells=args.cells, device=dev)
+    os.environ["SBX_SLAB_PATH"] = mode
+    slab = D.SlabScatter((n, n, n), synth.box_for(args.cells), cutoff=30, device=local)
+    os.environ.pop("SBX_SLAB_PATH", None)
     out = torch.empty(slab.n_shells, dtype=torch.float64, device=dev)
 
     def step():
@@ -469,45 +497,144 @@ def run_slab(args):
     with ClockSampler(local) as clk:
         step()
         ms = timed_steps(step, args.steps, args.warmup, world, dev)
-        slab.set_profiling(True)
+    slab.set_profiling(True)
+    stages = []
+    for _ in range(max(10, args.steps)):
+        barrier(world)  # every rank enters the profiled step together: no rank skew inside the collective's stage
         step()
         torch.cuda.synchronize()
-        prof = slab.profile()
-        slab.set_profiling(False)
+        stages.append(slab.profile())
+    slab.set_profiling(False)
+    prof = {k: float(np.mean([st[k] for st in stages])) for k in stages[0]}
+    prof = {k: max_over_ranks(v, world, dev) for k, v in prof.items()}
     I = out.cpu().numpy()
+    rec = {"path": "pruned_dft" if slab.path == 4 else "slab_fft", "ms_per_step": ms, "stage_ms": prof, "kernel": slab.kernel,
+           "n_shells": int(slab.n_shells), "clocks": clk.summary()}
+    q = slab.q.copy()
+    slab.close()
+    torch.cuda.empty_cache()
+    return rec, I, q
+
+
+def run_slab(args, modes=("pruned", "fft")):
+    """BASELINE config 5: ONE --grid^3 fp64 field, N0/world planes per rank.  Both decompositions behind
+    sbx_scatter_slab_execute are run through the real NCCL communicator: 'pruned' (each rank reduces its planes to the
+    mode sums, one small all-reduce) and 'fft' (cuFFT 2D -> NCCL all-to-all -> cuFFT 1D -> fused histogram ->
+    all-reduce, what north_star describes).  Strong scaling: the field is fixed, ranks split it."""
+    import torch
+
+    from simubox_b200 import distributed as D, synth
+
+    ctx = dist_setup(args.gpus)
+    rank, world, local = ctx
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    n = args.grid
+    lo, hi = D.slab_planes(n, rank, world)
+    # this rank's planes of the synthetic field, generated on the device plane block by plane block
+    local_slab = torch.empty((hi - lo, n, n), dtype=torch.float64, device=dev)
+    for x0 in range(lo, hi, 32):
+        x1 = min(hi, x0 + 32)
+        local_slab[x0 - lo:x1 - lo] = synth.field_planes_torch(3, (n, n, n), x0, x1, cells=args.cells, device=dev)
+    recs, rows = {}, {}
+    for mode in modes:
+        recs[mode], rows[mode], q = _slab_mode(args, mode, local_slab, ctx)
+    del local_slab
+    torch.cuda.empty_cache()
     if rank != 0:
-        slab.close()
-        return
+        return None
     peak, peak_src = measured_peak_gbs()
     spec = 16 * n * n * (n // 2 + 1)
-    pruned = slab.path == 4
-    # pruned DFT: the field is read once.  slab FFT: field + write/read of the half spectrum through the 2D stage,
-    # the exchange buffers and the 1D stage, then the scan
-    bytes_field = 8 * n ** 3 if pruned else 8 * n ** 3 + 6 * spec
-    kern = (slab.kernel or "pruned_blocked_kernel") if pruned else "cuFFT 2D + slab_pack_kernel + cuFFT 1D + shell_histogram_kernel"
-    comm = "all-reduce of the mode sums (no all-to-all)" if pruned else "NCCL all-to-all (send/recv group) + all-reduce"
-    print(json.dumps({
-        "metric": "density fields/sec (I(q), one slab-decomposed field)", "value": 1.0 / (ms * 1e-3), "unit": "fields/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True,
-        "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"one {n}^3 fp64 field, {world} slab(s) of {hi - lo} planes, cutoff=30", "grid": [n, n, n],
-                   "l2": f"{8 * n ** 3 / world / 1e9:.1f} GB per rank per pass exceed the 126 MB L2",
-                   "path": "pruned_dft_blocked" if pruned else "slab_fft", "parallelism": f"slab decomposition over {world} rank(s): {comm}"},
-        "stage_ms": prof, "n_shells": int(slab.n_shells), "dc_row": float(I[0]),
-        "roofline": {"bound": "hbm", "kernel": kern,
-                     "achieved": bytes_field / world / (ms * 1e-3) / 1e9, "peak": peak, "unit": "GB/s",
-                     "frac": bytes_field / world / (ms * 1e-3) / 1e9 / peak,
-                     "traffic": measured_traffic(f"{kern}|{n}^3|{world} slab(s)"), "peak_source": peak_src,
-                     "algorithmic_bytes_per_field": bytes_field},
-        "gpu_launches": (3 if pruned else 2) * args.steps, "clocks": clk.summary(),
-    }))
-    slab.close()
+    out = {"metric": "density fields/sec (I(q), one slab-decomposed field)", "unit": "fields/s", "n_gpus": world, "steps": args.steps,
+           "warmup": args.warmup, "higher_is_better": True, "scaling": "strong", "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+           "config": {"workload": f"one {n}^3 fp64 field, {world} slab(s) of {hi - lo} planes, cutoff=30", "grid": [n, n, n],
+                      "l2": f"{8 * n ** 3 / world / 1e9:.1f} GB per rank per pass exceed the 126 MB L2"},
+           "peak": peak, "peak_source": peak_src}
+    for mode, rec in recs.items():
+        pruned = rec["path"] == "pruned_dft"
+        # pruned DFT: the field is read once.  slab FFT: field + write/read of the half spectrum through the 2D stage,
+        # the exchange buffers and the 1D stage, then the scan
+        bytes_field = 8 * n ** 3 if pruned else 8 * n ** 3 + 6 * spec
+        rec["fields_per_s"] = 1.0 / (rec["ms_per_step"] * 1e-3)
+        rec["roofline"] = {"bound": "hbm", "kernel": (rec["kernel"] or "pruned_blocked_kernel") if pruned else "cuFFT 2D + slab_pack_kernel + cuFFT 1D + shell_histogram_kernel",
+                           "achieved": bytes_field / world / (rec["ms_per_step"] * 1e-3) / 1e9, "unit": "GB/s",
+                           "frac": bytes_field / world / (rec["ms_per_step"] * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_field": bytes_field}
+        rec["parallelism"] = ("all-reduce of the mode sums (no all-to-all)" if pruned else "NCCL all-to-all (send/recv group) + all-reduce")
+        if not pruned and world > 1 and rec["stage_ms"].get("all_to_all_ms"):
+            sent = spec / world * (world - 1) / world  # bytes each GPU sends (and receives)
+            rec["all_to_all_GBps_per_gpu"] = sent / (rec["stage_ms"]["all_to_all_ms"] * 1e-3) / 1e9
+    if len(rows) == 2:
+        a, b = rows["pruned"], rows["fft"]
+        full = len(a) - 1
+        tol = 1e-9 * np.abs(a[:full]) + 1e-12 * np.abs(a[1:]).max()
+        out["slab_parity"] = bool(np.all(np.abs(a[:full] - b[:full]) <= tol))
+        out["slab_parity_worst_rel"] = float(np.max(np.abs(a[:full] - b[:full]) / np.maximum(np.abs(a[:full]), 1e-300)))
+    first = recs[modes[0]]
+    out.update(value=first["fields_per_s"], ms_per_step=first["ms_per_step"], modes=recs, dc_row=float(rows[modes[0]][0]),
+               gpu_launches=(3 if first["path"] == "pruned_dft" else 2) * args.steps, clocks=first["clocks"],
+               roofline=dict(first["roofline"], peak=peak, peak_source=peak_src, traffic=measured_traffic(f"{first['roofline']['kernel']}|{n}^3|{world} slab(s)")))
+    return out
+
+
+# ----------------------------------------------------------------------------- one Voronoi grid across GPUs (voxel slabs)
+def run_voronoi_sharded(args, grids=((256, 16), (512, 32))):
+    """ONE grid labelled by voxel slab, seeds replicated, no collective; strong scaling against the
+    single-launch labelling of the whole grid on one GPU.  Each rank checks its slab against its planes of a whole-grid
+    labelling (bit for bit)."""
+    import torch
+
+    from simubox_b200 import VoronoiCell, distributed as D, synth
+
+    rank, world, local = dist_setup(args.gpus)
+    dev = torch.device("cuda", local)
+    torch.cuda.set_device(dev)
+    flush = torch.empty(1 << 29, dtype=torch.uint8, device=dev)
+    recs = []
+    for n, per_axis in grids:
+        shape, box = (n, n, n), (float(n),) * 3
+        pts = torch.from_numpy(synth.seeds_lattice(shape, per_axis, 4.0, 1234)).to(dev)
+        mask = (synth.fields_torch(1, 1, shape, cells=max(1, n // 64), device=dev)[0] > 0.5).to(torch.uint8).contiguous()
+        lo, hi = D.shard_range(n, rank, world)
+        mslab = mask[lo:hi].contiguous()
+
+        def timed(fn):
+            for _ in range(3):
+                flush.zero_(); fn()
+            barrier(world)
+            pairs = []
+            for _ in range(args.steps):
+                flush.zero_()
+                e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+                e0.record(); fn(); e1.record()
+                pairs.append((e0, e1))
+            torch.cuda.synchronize()
+            t = float(np.median([x.elapsed_time(y) for x, y in pairs]))
+            barrier(world)
+            return max_over_ranks(t, world, dev)
+
+        last = {}
+        ms = timed(lambda: last.__setitem__("slab", VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mslab, device=local, return_tensor=True, planes=(lo, hi))))
+        whole_ms = timed(lambda: last.__setitem__("whole", VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, device=local, return_tensor=True)))
+        ok = torch.equal(last["slab"], last["whole"][lo:hi])
+        ok_all = max_over_ranks(0.0 if ok else 1.0, world, dev) == 0.0
+        recs.append({"grid": [n, n, n], "seeds": per_axis ** 3, "planes_per_rank": hi - lo, "ms_per_grid": ms, "voxels_per_s": n ** 3 / (ms * 1e-3),
+                     "one_gpu_whole_grid_ms": whole_ms, "speedup_vs_one_gpu": whole_ms / ms, "slabs_equal_whole_grid": bool(ok_all)})
+        del mask, mslab, last
+        torch.cuda.empty_cache()
+    del flush
+    torch.cuda.empty_cache()
+    if rank != 0:
+        return None
+    return {"metric": "Voronoi voxels/sec, one grid sharded by voxel slab", "unit": "voxels/s", "n_gpus": world, "scaling": "strong",
+            "parallelism": f"planes [r N0/P, (r+1) N0/P) on rank r of {world}, seeds replicated, no collective (sbx_voronoi_plan_execute_range)",
+            "l2": "512 MiB buffer written before every timed labelling", "steps": args.steps, "grids": recs}
 
 
 # ----------------------------------------------------------------------------- phase-diagram sweep (config 4)
 def run_sweep(args):
     """BASELINE config 4: a sweep of 256^3 fields sharded over the GPUs; per field scatter I(q)+peaks AND periodic
-    Voronoi labelling of its masked grid with 4096 domain-centre seeds.  --fields = fields per GPU (weak scaling)."""
+    Voronoi labelling of its masked grid with 4096 domain-centre seeds.  --sweep-fields = fields per GPU (weak scaling;
+    256 per GPU = the 2048 fields of the config on 8 GPUs)."""
     import torch
 
     from simubox_b200 import Scatter, VoronoiCell, synth
@@ -515,41 +642,50 @@ def run_sweep(args):
     rank, world, local = dist_setup(args.gpus)
     dev = torch.device("cuda", local)
     torch.cuda.set_device(dev)
-    n, cells, B = args.vgrid, 4, args.fields
+    n, cells, B = args.vgrid, 4, args.sweep_fields
     shape, L = (n, n, n), synth.box_for(cells)
     fields = torch.empty((B, *shape), dtype=torch.float64, device=dev)
     masks = torch.empty((B, *shape), dtype=torch.uint8, device=dev)
     for b in range(B):
         fields[b] = synth.fields_torch(rank * B + b, 1, shape, cells=cells, device=dev)[0]
         masks[b] = (fields[b] > 0.5).to(torch.uint8)
-    seeds = [torch.from_numpy(synth.seeds_lattice(shape, 16, 4.0, 77 + rank * B + b)).to(dev) for b in range(min(B, 16))]
+    # every field has its own seed set (default_rng(1234 + i))
+    seeds = torch.from_numpy(np.stack([synth.seeds_lattice(shape, 16, 4.0, 1234 + rank * B + b) for b in range(B)])).to(dev)
     kw = dict(cutoff=30, threshold=1e-12, peaks=True, width=PEAK_KW["width"], step=PEAK_KW["step"], peak_cutoff=PEAK_KW["cutoff"],
               min_height=PEAK_KW["min_height"], max_batch=min(32, B), device=local)
     box = (float(n),) * 3
     last = {}
+    checks = torch.zeros(B, dtype=torch.int64, device=dev)
 
     def step():
         last["scatter"] = Scatter.sacttering_peak_batch(fields, L, **kw)
         for b in range(B):
-            last["lab"] = VoronoiCell.label_grid(seeds[b % len(seeds)], 0, shape=shape, box=box, mask=masks[b], device=local, return_tensor=True)
+            lab = VoronoiCell.label_grid(seeds[b], 0, shape=shape, box=box, mask=masks[b], device=local, return_tensor=True)
+            if b == B - 1:
+                last["lab"] = lab
 
+    steps = max(2, min(args.steps, 5))
     with ClockSampler(local) as clk:
-        ms = timed_steps(step, args.steps, args.warmup, world, dev)
+        ms = timed_steps(step, steps, 3, world, dev)
+    checks[0] = last["lab"].to(torch.int64).sum()  # nothing large leaves the device
+    del fields, masks
+    torch.cuda.empty_cache()
     if rank != 0:
-        return
+        return None
     peak, peak_src = measured_peak_gbs()
     bytes_field = 8 * n ** 3 + (4 * n ** 3 + 32 * 4096 + n ** 3)  # field read once + labels, seeds, mask
-    print(json.dumps({
+    return {
         "metric": "sweep fields/sec (I(q)+peaks and Voronoi labelling per field)", "value": B * world / (ms * 1e-3), "unit": "fields/s",
-        "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
+        "n_gpus": world, "steps": steps, "warmup": 3, "ms_per_step": ms, "higher_is_better": True, "scaling": "weak",
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
-        "config": {"workload": f"{B} synthetic {n}^3 fields per GPU: scatter cutoff=30 + show_peak, and periodic Voronoi labels (4096 seeds, uint8 mask) per field",
+        "config": {"workload": f"{B} synthetic {n}^3 fields per GPU ({B * world} in all), own seed set per field: scatter cutoff=30 + show_peak, and periodic Voronoi labels (4096 seeds, uint8 mask) per field",
                    "l2": f"{B * 8 * n ** 3 / 1e9:.1f} GB of fields per pass exceed the 126 MB L2", "parallelism": f"fields sharded, {world} rank(s), no collective"},
         "roofline": {"bound": "hbm", "kernel": "pruned_ring_kernel + coarse/mid/label kernels", "achieved": bytes_field * B / (ms * 1e-3) / 1e9,
                      "peak": peak, "unit": "GB/s", "frac": bytes_field * B / (ms * 1e-3) / 1e9 / peak, "traffic": None, "peak_source": peak_src,
                      "algorithmic_bytes_per_field": bytes_field},
-        "gpu_launches": args.steps * (-(-B // min(32, B)) + 3 * B), "clocks": clk.summary(),
-    }))
+        "label_checksum_last_field": int(checks[0].item()),
+        "gpu_launches": steps * (-(-B // min(32, B)) + 3 * B), "clocks": clk.summary(),
+    }
 
 
 # ----------------------------------------------------------------------------- reference arm
@@ -580,7 +716,8 @@ def run_reference(args):
         "impl": "reference", "metric": metric, "value": rate, "unit": unit, "n_gpus": args.gpus, "steps": steps, "warmup": warm,
         "ms_per_step": per_step / rate * 1e3, "higher_is_better": True, "scaling": "weak", "vs_baseline": None, "dtype": "f64",
         "data": "synthetic", "config": {"workload": workload, "bounded_sample": sample},
-        "cpu_baseline": {"value": rate, "unit": unit, "cores": cores, "kind": "port", "sample": sample},
+        "cpu_baseline": {"value": rate, "unit": unit, "cores": cores, "kind": "port", "txyz": "vectorised", "sample": sample,
+                         "note": "same generator and per-unit work as the GPU arm's config, timed on a bounded sample per step (per-unit rate); numpy port of the reference with a vectorised txyz (~3.6x faster per core than the reference itself)"},
         "e2e": {"value": rate, "unit": unit, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }))
@@ -604,6 +741,9 @@ def main():
     ap.add_argument("--vgrid", type=int, default=256)
     ap.add_argument("--vgrids", type=int, default=1)
     ap.add_argument("--cpu-voxels", type=int, default=4096)
+    ap.add_argument("--sweep-fields", type=int, default=256, help="256^3 fields per GPU of the sweep record (config 4: 2048 over 8 GPUs)")
+    ap.add_argument("--slab-grid", type=int, default=1024, help="grid of the one-field slab record (config 5)")
+    ap.add_argument("--sub", default="all", help="sub-records of the default line: all | none | comma list of voronoi,sweep,slab,voronoi_sharded")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     if args.impl == "reference":
@@ -611,15 +751,46 @@ def main():
     from simubox_b200 import build
 
     build.build()
+    world = int(os.environ.get("WORLD_SIZE", "1"))
     if args.workload == "voronoi":
-        run_voronoi(args)
+        rec = run_voronoi(args)
     elif args.workload == "slab":
-        run_slab(args)
+        rec = run_slab(args)
     elif args.workload == "sweep":
-        run_sweep(args)
+        rec = run_sweep(args)
     else:
-        run_scatter(args)
-    if int(os.environ.get("WORLD_SIZE", "1")) > 1:
+        rec = run_scatter(args)
+        want = {"voronoi", "sweep", "slab", "voronoi_sharded"} if args.sub == "all" else set(filter(None, args.sub.split(","))) - {"none"}
+        subs = {}
+        sub_args = argparse.Namespace(**vars(args))
+        sub_args.steps, sub_args.e2e_steps = min(args.steps, 10), min(args.e2e_steps, 2)
+
+        def leg(name, fn):
+            # a failing leg must not take the headline down with it: the error is recorded in its place
+            t0 = time.time()
+            try:
+                r = fn()
+            except Exception as e:  # noqa: BLE001
+                r = {"error": f"{type(e).__name__}: {e}"[:300]}
+            if isinstance(r, dict):
+                r["leg_seconds"] = round(time.time() - t0, 1)
+            subs[name] = r
+
+        if "voronoi" in want:
+            leg("voronoi", lambda: run_voronoi(sub_args))
+        if "voronoi_sharded" in want and world > 1:
+            leg("voronoi_sharded", lambda: run_voronoi_sharded(sub_args))
+        if "slab" in want and world > 1:
+            slab_args = argparse.Namespace(**vars(sub_args))
+            slab_args.grid, slab_args.cells = args.slab_grid, 8
+            leg("slab", lambda: run_slab(slab_args))
+        if "sweep" in want:
+            leg("sweep", lambda: run_sweep(sub_args))
+        if rec is not None:
+            rec.update({k: v for k, v in subs.items() if v is not None})
+    if rec is not None:
+        print(json.dumps(rec))
+    if world > 1:
         import torch.distributed as dist
 
         dist.destroy_process_group()
