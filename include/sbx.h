@@ -169,7 +169,8 @@ int sbx_voronoi_plan_destroy(sbx_voronoi_plan* plan);
  *   sbx_nccl_unique_id on rank 0 -> broadcast the SBX_NCCL_ID_BYTES bytes by any means
  *   (torch.distributed, MPI, a file) -> sbx_nccl_comm_create on every rank.
  * NCCL is loaded at run time with dlopen (the copy already in the process, else $SBX_NCCL_LIB,
- * else libnccl.so.2).  N0 and N1 must be divisible by `world`.
+ * else libnccl.so.2).  N0 must be divisible by `world`; the slab FFT mode
+ * (not the pruned mode) needs N1 divisible by `world` as well.
  * local_slab = planes [rank*N0/world, (rank+1)*N0/world) of the field (fp64, C order);
  * shell_I: n_shells fp64, identical on all ranks after the call completes on `stream`. */
 #define SBX_NCCL_ID_BYTES 128
@@ -239,8 +240,10 @@ int sbx_particle_splat(int device, const double* xyz, const int32_t* type, int64
 /* ---- phin / phout text reader (host code, no device needed) ---------------------------------
  * Replaces pd.read_csv(path, skiprows=skip, header=None, sep="[ ]+", engine="python")
  * (SimuBox/toolkit/reader.py:170-172).  buf = the whole file in host memory.  `skip` header lines are
- * skipped, blank lines ignored, tokens are blank-separated and converted with correctly rounded
- * decimal->double conversion (the doubles Python's float() gives).  threads <= 0: one per core.
+ * skipped, blank lines ignored, tokens are blank-separated and converted with the arithmetic of
+ * pandas' precise_xstrtod (what that read_csv call uses: <= 17 digits accumulated in a double, then one multiply or
+ * divide by a power of ten -- NOT correctly rounded beyond 15 digits, and deliberately so: the doubles are the
+ * reference's bit for bit).  threads <= 0: one per core.
  * shape: rows = non-blank lines after the header, cols = tokens of the first of them.
  * parse: out = rows x cols fp64, C order; SBX_EINVAL when a row has another width or a token is not a
  * number (the Python layer raises ValueError, which drives the reference's header-guess retry,

@@ -438,10 +438,12 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
                 kMaxDynSmem / 24);
   }
 
-  // fields per cuFFT launch: keep field + spectrum of one chunk inside the 126 MB L2
-  const size_t per_field = (size_t)g.nreal * 8 + (size_t)g.nspec * 16;
-  size_t chunk = (size_t)64 << 20;
-  chunk = std::max<size_t>(1, chunk / per_field);
+  // fields per cuFFT launch and per histogram launch: a batched plan over as many fields as 1 GiB of half spectra holds
+  // (at most 64).  r01 sized this to the L2 (one 128^3 field per cuFFT exec, one histogram launch per field: 512 launches
+  // per 256 fields, each ending in the serial peak search of its last CTA); the row-wise histogram no longer reads
+  // the rows beyond the shell table, so L2 residency of the spectrum buys nothing and batching buys the launches back.
+  size_t chunk = ((size_t)1 << 30) / ((size_t)g.nspec * 16);
+  chunk = std::min<size_t>(std::max<size_t>(1, chunk), 64);
   if (path == SBX_SCATTER_FFT_GATHER) chunk = (size_t)max_batch;  // one CTA per field: launch many fields at once
   if (const char* e = getenv("SBX_FFT_CHUNK")) chunk = std::max(1, atoi(e));
   p->chunk = (int)std::min<size_t>(chunk, (size_t)max_batch);

@@ -154,8 +154,8 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
   if (!out || !N || !L) return fail(SBX_EINVAL, "NULL argument");
   *out = nullptr;
   if (world < 1 || rank < 0 || rank >= world) return fail(SBX_EINVAL, "rank %d / world %d out of range", rank, world);
-  if (N[0] % world || N[1] % world)
-    return fail(SBX_EINVAL, "N0=%lld and N1=%lld must be divisible by the number of ranks (%d)", (long long)N[0], (long long)N[1], world);
+  if (N[0] % world)
+    return fail(SBX_EINVAL, "N0=%lld must be divisible by the number of ranks (%d)", (long long)N[0], world);
   int rc = require_sm100(device);
   if (rc) return rc;
   DeviceGuard guard(device);
@@ -177,14 +177,21 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
     const char* sp = getenv("SBX_SLAB_PATH");
     const bool want_fft = sp && !strcmp(sp, "fft"), want_pruned = sp && !strcmp(sp, "pruned");
     if (!want_fft) {
+      // The mode must come out the same on every rank, or their collectives no longer match: it may depend on the
+      // geometry only (shell modes, grid, planes per rank -- SBX_EINVAL from the inner plan, identical everywhere).
+      // Any other failure of the inner plan (allocation, CUDA) is an error of this rank, not a reason to change mode.
       sbx_scatter_plan* inner = nullptr;
-      if (sbx_scatter_plan_create_ex(&inner, device, 3, N, L, cutoff, threshold, 1, SBX_SCATTER_PRUNED_FUSED) == SBX_OK) {
+      const int irc = sbx_scatter_plan_create_ex(&inner, device, 3, N, L, cutoff, threshold, 1, SBX_SCATTER_PRUNED_FUSED);
+      if (irc == SBX_OK) {
         if (scatter_slab_supported(inner, p->n0)) {
           p->inner = inner;
           p->pruned = true;
         } else {
           sbx_scatter_plan_destroy(inner);
         }
+      } else if (irc != SBX_EINVAL) {
+        slab_free(p);
+        return irc;
       }
       if (want_pruned && !p->pruned) {
         slab_free(p);
@@ -204,6 +211,10 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
     }
   }
 
+  if (N[1] % world) {  // only the transpose of the slab FFT splits axis 1
+    slab_free(p);
+    return fail(SBX_EINVAL, "slab FFT mode: N1=%lld must be divisible by the number of ranks (%d)", (long long)N[1], world);
+  }
   // k^2 tables: same construction as the single-GPU plan (scatter.cu build_device_tables)
   GridDev& g = p->grid;
   g.ndim = 3;

@@ -89,11 +89,15 @@ class Scatter:
                               max_batch: int = 16, device: int = 0, path: int = _lib.PATH_AUTO):
         """Many fields of one grid.  ``fields``: (B, *N) fp64 -- a numpy array (host; pinned or
         not) is streamed to the GPU in chunks with copy/compute overlap, a CUDA tensor is used
-        in place.  Returns dict(q, I (B, n_shells), [peak_idx (B, max_peaks), n_peaks (B)])."""
+        in place (the plan is then taken on the tensor's device, whatever ``device`` says).  Plans are cached per
+        (grid, box, cutoff, batch, device, path) and own one workspace: use one stream / thread per plan.
+        Returns dict(q, I (B, n_shells), [peak_idx (B, max_peaks), n_peaks (B)])."""
         torch = torch_cuda()
         is_tensor = isinstance(fields, torch.Tensor)
         shape = tuple(fields.shape)
         B, N = int(shape[0]), shape[1:]
+        if is_tensor and fields.is_cuda:
+            device = fields.device.index  # the plan (tables, workspace, stream) must live where the data is
         plan = get_plan(N, lxlylz, cutoff, threshold, max_batch=min(max_batch, B), device=device, path=path)
         L_ = _lib.lib()
         res = {"q": plan.q.copy(), "path": _lib.PATH_NAMES.get(plan.path, "?")}
