@@ -161,6 +161,20 @@ int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* plan, const double* seeds, 
                                    const uint8_t* mask, int32_t* labels, int64_t x_lo, int64_t x_hi,
                                    void* stream, int64_t* stats_host);
 int sbx_voronoi_plan_destroy(sbx_voronoi_plan* plan);
+/* Allocation-free labelling.  NO COUNTERPART IN THE REFERENCE: added for callers
+ * that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as
+ * sbx_voronoi_plan_execute_range with weights = NULL, mode = 0 (additive), bit for bit; it calls no cudaMalloc /
+ * cudaFree / allocating library routine.  Its scratch (sorted image points, cell counters, cell start table) is one
+ * file-scope device array of 12 MiB that every GPU loading this library holds until exit, which sets the limits:
+ *   S x (27 | 9 | 1 images for periodic 3D | periodic 2D | non-periodic) <= 262144 image points
+ *   (4096 seeds in a periodic 3D box use 110592) and at most 262144 cells of the internal cell list;
+ * beyond either the call returns SBX_ERANGE and names the plan entry point to use instead.  Asynchronous on `stream`.
+ * All calls share the array: calls that overlap on one GPU (other streams or threads) race on it -- issue them in
+ * stream order.  The first call on a device resolves the array's address (cudaGetSymbolAddress): make it outside
+ * graph capture. */
+int sbx_voronoi_label_noalloc(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
+                              const double* box_host, const uint8_t* mask, int32_t* labels, int64_t x_lo,
+                              int64_t x_hi, void* stream);
 
 /* ---- one giant field across GPUs: slab-decomposed FFT + NCCL all-to-all ---------------
  * The reference cannot run a 1024^3 field (scatter.py:82-97 materialises ~300 B/voxel); its only

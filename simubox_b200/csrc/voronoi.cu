@@ -1158,3 +1158,106 @@ extern "C" int sbx_voronoi_label(int device, int ndim, const int64_t* N, const d
   sbx_voronoi_plan_destroy(p);
   return rc;
 }
+
+// ---------------------------------------------------------------------------------------------------------------
+// Allocation-free labelling (no counterpart in the reference; added for callers
+// that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The cell-list path above needs three pieces of scratch: the sorted image points, the cell counters and the cell
+// start table.  Here they live in ONE file-scope device array of fixed size, which every GPU that loads this library
+// holds until the process exits:
+//     image points  kNaMaxPoints x 32 B = 8 MiB   (seeds x enumerated periodic images: S x 3^d, S when non-periodic)
+//     counters      3 x kNaMaxCells ints = 3 MiB   (count | cursor | rowcount, 2 ncell + nrow <= 3 ncell)
+//     start table   (kNaMaxCells + 64) ints = 1 MiB
+// In HOST code the array's name is only a stand-in for the symbol, not a device address: its address is taken once
+// per device, with that device current, by cudaGetSymbolAddress, and that pointer is what the kernels get.
+// All calls share the array and it keeps the last call's contents: the counters are cleared at the start of every
+// call (cudaMemsetAsync on the caller's stream: no allocation), everything else is written before it is read.  Calls
+// that overlap on one GPU (two streams, two threads) race on it -- issue them in stream order.
+// ---------------------------------------------------------------------------------------------------------------
+namespace {
+constexpr long long kNaMaxPoints = 1ll << 18;
+constexpr long long kNaMaxCells = 1ll << 18;
+constexpr size_t kNaPtsBytes = (size_t)kNaMaxPoints * sizeof(SeedRec);
+constexpr size_t kNaCntBytes = (size_t)3 * kNaMaxCells * sizeof(int);
+constexpr size_t kNaStartBytes = (size_t)(kNaMaxCells + 64) * sizeof(int);
+constexpr size_t kNaBytes = kNaPtsBytes + kNaCntBytes + kNaStartBytes;
+constexpr int kNaMaxDevices = 64;
+}  // namespace
+
+static __device__ __align__(256) unsigned char g_noalloc_scratch[kNaBytes];
+
+#include <mutex>
+
+// device address of g_noalloc_scratch on `device` (which must be current); resolved once per device
+static int noalloc_scratch(int device, unsigned char** out) {
+  static std::mutex mu;
+  static unsigned char* ptrs[kNaMaxDevices] = {};
+  if (device < 0 || device >= kNaMaxDevices) return fail(SBX_EINVAL, "device %d outside the %d the static scratch table covers", device, kNaMaxDevices);
+  std::lock_guard<std::mutex> lock(mu);
+  if (!ptrs[device]) {
+    unsigned char* p = nullptr;
+    const cudaError_t e = cudaGetSymbolAddress((void**)&p, g_noalloc_scratch);
+    if (e != cudaSuccess || !p) return fail(SBX_ECUDA, "cudaGetSymbolAddress(static Voronoi scratch) on device %d: %s", device, cudaGetErrorString(e));
+    ptrs[device] = p;
+  }
+  *out = ptrs[device];
+  return SBX_OK;
+}
+
+extern "C" int sbx_voronoi_label_noalloc(int device, int ndim, const int64_t* N, const double* seeds, int64_t S,
+                                         const double* box_host, const uint8_t* mask, int32_t* labels, int64_t x_lo,
+                                         int64_t x_hi, void* stream) {
+  if (!N || !seeds || !labels) return fail(SBX_EINVAL, "NULL argument");
+  if (ndim != 2 && ndim != 3) return fail(SBX_EINVAL, "ndim must be 2 or 3, got %d", ndim);
+  if (S < 1) return fail(SBX_EINVAL, "seed count %lld out of range", (long long)S);
+  const long long images = box_host ? (ndim == 3 ? 27 : 9) : 1;
+  if ((long long)S > kNaMaxPoints / images)
+    return fail(SBX_ERANGE, "%lld seeds x %lld periodic images exceed the %lld image points of the static scratch; use sbx_voronoi_plan_execute_range",
+                (long long)S, images, kNaMaxPoints);
+  int rc = require_sm100(device);
+  if (rc) return rc;
+  // geometry exactly as sbx_voronoi_plan_create + sbx_voronoi_plan_execute_range set it up, on the stack
+  sbx_voronoi_plan tmp;
+  tmp.device = device;
+  tmp.ndim = ndim;
+  VorGeo& g = tmp.g;
+  g = VorGeo{};
+  g.nd = ndim;
+  const int off = 3 - ndim;
+  for (int a = 0; a < 3; ++a) { g.N[a] = 1; g.box[a] = 1.0; }
+  for (int a = 0; a < ndim; ++a) {
+    if (N[a] < 1 || N[a] > (1 << 20)) return fail(SBX_EINVAL, "N[%d]=%lld out of range", a, (long long)N[a]);
+    g.N[a + off] = (int)N[a];
+  }
+  g.mode = 0;
+  g.S = S;
+  g.periodic = box_host ? 1 : 0;
+  for (int a = 0; a < ndim && box_host; ++a) {
+    if (!(box_host[a] > 0.0)) return fail(SBX_EINVAL, "box[%d] must be > 0", a);
+    g.box[a + off] = box_host[a];
+  }
+  const int64_t N0 = g.N[off];
+  if (x_lo < 0 || x_hi > N0 || x_lo >= x_hi) return fail(SBX_EINVAL, "plane range [%lld, %lld) outside [0, %lld)", (long long)x_lo, (long long)x_hi, (long long)N0);
+  CellGeo c{};
+  cell_geometry(&tmp, g, S, (int)x_lo, (int)x_hi, c);
+  if (c.ncell > kNaMaxCells)
+    return fail(SBX_ERANGE, "%d cells exceed the %lld cells of the static scratch; use sbx_voronoi_plan_execute_range", c.ncell, kNaMaxCells);
+  if (c.nt[0] > 65535 || c.nt[1] > 65535) return fail(SBX_EINVAL, "grid too large for the cell path");
+  DeviceGuard guard(device);
+  unsigned char* base = nullptr;
+  if ((rc = noalloc_scratch(device, &base))) return rc;
+  SeedRec* pts = reinterpret_cast<SeedRec*>(base);
+  int* counters = reinterpret_cast<int*>(base + kNaPtsBytes);
+  int* start = reinterpret_cast<int*>(base + kNaPtsBytes + kNaCntBytes);
+  cudaStream_t st = (cudaStream_t)stream;
+  SBX_CUDA(cudaMemsetAsync(counters, 0, (size_t)(2ll * c.ncell + c.nrow) * sizeof(int), st));  // whatever the last call left
+  if (ndim == 3) {
+    if (g.periodic) launch_cells<3, true>(c, seeds, counters, start, pts, mask, labels, nullptr, st);
+    else launch_cells<3, false>(c, seeds, counters, start, pts, mask, labels, nullptr, st);
+  } else {
+    if (g.periodic) launch_cells<2, true>(c, seeds, counters, start, pts, mask, labels, nullptr, st);
+    else launch_cells<2, false>(c, seeds, counters, start, pts, mask, labels, nullptr, st);
+  }
+  SBX_CUDA(cudaGetLastError());
+  return SBX_OK;
+}
