@@ -476,7 +476,7 @@ def run_voronoi(args):
 
 
 # ----------------------------------------------------------------------------- one giant field, slab decomposed
-def _slab_mode(args, mode, local_slab, ctx):
+def _slab_mode(args, mode, local_slab, ctx, env=None):
     """One mode of the slab-decomposed scatter ('pruned' or 'fft') on this rank's planes: ms per step (CUDA events, max
     over ranks), stage split averaged over >= 10 profiled steps each started at a barrier, the rows."""
     import torch
@@ -486,9 +486,11 @@ def _slab_mode(args, mode, local_slab, ctx):
     rank, world, local = ctx
     dev = torch.device("cuda", local)
     n = args.grid
-    os.environ["SBX_SLAB_PATH"] = mode
+    env = dict(env or {}, SBX_SLAB_PATH=mode)
+    os.environ.update(env)  # read by the library at plan creation
     slab = D.SlabScatter((n, n, n), synth.box_for(args.cells), cutoff=30, device=local)
-    os.environ.pop("SBX_SLAB_PATH", None)
+    for k in env:
+        os.environ.pop(k, None)
     out = torch.empty(slab.n_shells, dtype=torch.float64, device=dev)
 
     def step():
@@ -539,6 +541,12 @@ def run_slab(args, modes=("pruned", "fft")):
     recs, rows = {}, {}
     for mode in modes:
         recs[mode], rows[mode], q = _slab_mode(args, mode, local_slab, ctx)
+    if "fft" in modes and world > 1:
+        # the exchange-bound form of the same mode: every column of the half spectrum travels (what a cutoff that
+        # reaches the Nyquist column needs), with the chunked exchange overlapped (default) and unchunked
+        recs["fft_allcols"], rows["fft_allcols"], q = _slab_mode(args, "fft", local_slab, ctx, {"SBX_SLAB_ALLCOLS": "1"})
+        recs["fft_allcols_unchunked"], rows["fft_allcols_unchunked"], q = _slab_mode(args, "fft", local_slab, ctx, {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_CHUNKS": "1"})
+        recs["fft_allcols_chunks8"], rows["fft_allcols_chunks8"], q = _slab_mode(args, "fft", local_slab, ctx, {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_CHUNKS": "8"})
     del local_slab
     torch.cuda.empty_cache()
     if rank != 0:
@@ -561,14 +569,24 @@ def run_slab(args, modes=("pruned", "fft")):
                            "frac": bytes_field / world / (rec["ms_per_step"] * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_field": bytes_field}
         rec["parallelism"] = ("all-reduce of the mode sums (no all-to-all)" if pruned else "NCCL all-to-all (send/recv group) + all-reduce")
         if not pruned and world > 1 and rec["stage_ms"].get("all_to_all_ms"):
-            sent = spec / world * (world - 1) / world  # bytes each GPU sends (and receives)
-            rec["all_to_all_GBps_per_gpu"] = sent / (rec["stage_ms"]["all_to_all_ms"] * 1e-3) / 1e9
-    if len(rows) == 2:
+            allc = mode.startswith("fft_allcols")
+            rec["columns_exchanged"] = "all (N2/2+1)" if allc else "only c with kv2[c] <= largest listed k^2"
+            if allc:
+                sent = spec / world * (world - 1) / world  # bytes each GPU sends (and receives)
+                rec["all_to_all_GBps_per_gpu"] = sent / (rec["stage_ms"]["all_to_all_ms"] * 1e-3) / 1e9
+            # stage_ms comes from serialised (profiled) steps; ms_per_step from the pipelined ones
+            serial = sum(rec["stage_ms"].values())
+            rec["serial_stage_sum_ms"] = serial
+            rec["all_to_all_hidden_frac"] = max(0.0, min(1.0, (serial - rec["ms_per_step"]) / rec["stage_ms"]["all_to_all_ms"]))
+    if "pruned" in rows and "fft" in rows:
         a, b = rows["pruned"], rows["fft"]
         full = len(a) - 1
         tol = 1e-9 * np.abs(a[:full]) + 1e-12 * np.abs(a[1:]).max()
         out["slab_parity"] = bool(np.all(np.abs(a[:full] - b[:full]) <= tol))
         out["slab_parity_worst_rel"] = float(np.max(np.abs(a[:full] - b[:full]) / np.maximum(np.abs(a[:full]), 1e-300)))
+        for extra in ("fft_allcols", "fft_allcols_unchunked", "fft_allcols_chunks8"):
+            if extra in rows:
+                out["slab_parity"] = bool(out["slab_parity"] and np.all(np.abs(a[:full] - rows[extra][:full]) <= tol))
     first = recs[modes[0]]
     out.update(value=first["fields_per_s"], ms_per_step=first["ms_per_step"], modes=recs, dc_row=float(rows[modes[0]][0]),
                gpu_launches=(3 if first["path"] == "pruned_dft" else 2) * args.steps, clocks=first["clocks"],

@@ -170,6 +170,7 @@ static int build_device_tables(sbx_scatter_plan* p) {
   g.N0 = (int)t.N[0]; g.N1 = (int)t.N[1]; g.N2 = (int)t.N[2];
   const int64_t nlast = t.N[t.ndim - 1];
   g.H = (int)(nlast / 2 + 1);
+  g.Hs = g.H;
   g.nreal = t.total();
   g.nspec = g.nreal / nlast * g.H;
   g.factor = 1.0 / (double)g.nreal;

@@ -74,7 +74,7 @@ shell_histogram_kernel(const double2* __restrict__ spec, GridDev g, ShellDev sh,
 
   if (NDIM == 3) {
     const int lane = tid & 31;
-    const long long nrows = g.nspec / g.H;  // local rows (slab layout: N0 * n1loc)
+    const long long nrows = g.nspec / g.Hs;  // local rows (slab layout: N0 * n1loc), Hs stored columns each
     const long long wglobal = (long long)blockIdx.x * (blockDim.x >> 5) + (tid >> 5), wtotal = (long long)gridDim.x * (blockDim.x >> 5);
     for (long long r0 = wglobal * 32; r0 < nrows; r0 += wtotal * 32) {
       const long long lrow = r0 + lane;
@@ -93,13 +93,13 @@ shell_histogram_kernel(const double2* __restrict__ spec, GridDev g, ShellDev sh,
         todo &= todo - 1;
         const long long wl = r0 + src, wrow = __shfl_sync(0xffffffffu, row, src);
         const double px = __shfl_sync(0xffffffffu, p2.x, src), py = __shfl_sync(0xffffffffu, p2.y, src);
-        for (int c = lane; c < g.H; c += 32) {
+        for (int c = lane; c < g.Hs; c += 32) {
           const double kc = g.kvlast[c];
           const double v1 = __dadd_rn(px, kc), v2 = __dadd_rn(py, kc);
           const bool has_mirror = (c != 0) && (c != halfLast);
           const bool h1 = v1 <= sh.vcut, h2 = has_mirror && v2 <= sh.vcut;
           if (!(h1 || h2)) continue;
-          const double inten = intensity(fs[wl * g.H + c], g.factor);
+          const double inten = intensity(fs[wl * g.Hs + c], g.factor);
           if (h1) {
             const int s = shell_of(sh, rep_s, v1, wrow * g.N2 + c);
             if (s >= 0) { atomicAdd(&bins[s], inten); any = true; }

@@ -17,7 +17,8 @@ struct ShellDev {
 struct GridDev {
   int ndim;
   int N0, N1, N2;      // unused trailing dims = 1
-  int H;               // stored length of the last axis = N_last/2 + 1
+  int H;               // half-spectrum length of the last axis = N_last/2 + 1 (c = H - 1 is the Nyquist column)
+  int Hs;              // 3D: columns STORED per row, c < Hs <= H (slab FFT mode exchanges only the columns that can hold a listed mode)
   long long nspec;     // stored elements per field
   long long nreal;     // real samples per field
   const double2* plane2;  // 3D: per (a,b) row {plane k^2 of F[a,b,.], plane k^2 of its mirror row}

@@ -6,12 +6,18 @@
 // (work/.../ABC_star/abc_star_short.c:270-286).  B200 layout, one process per GPU:
 //
 //   rank r owns planes x in [r*n0, (r+1)*n0) of the N0 x N1 x N2 field           (n0 = N0/P)
-//   A  cuFFT 2D D2Z over (y,z), batch n0        X[x][j][c]          c < H = N2/2+1
-//      pack by destination rank                 Y[d][x][jl][c]      j = d*n1 + jl  (n1 = N1/P)
-//   X  all-to-all (ncclSend/ncclRecv group)     X[s][x][jl][c] = X[x_global][jl][c]
-//   B  cuFFT 1D Z2Z along x (stride n1*H)       full spectrum for columns j in [r*n1,(r+1)*n1)
+//   A  cuFFT 2D D2Z over (y,z), K chunks of n0/K planes     F[x][j][c]     c < H = N2/2+1
+//      pack by destination rank, columns c < Hc only        Y[d][x][jl][c] j = d*n1 + jl  (n1 = N1/P)
+//   X  all-to-all (ncclSend/ncclRecv group per chunk)       X[s][x][jl][c] = spectrum of plane s*n0 + x
+//   B  cuFFT 1D Z2Z along x (stride n1*Hc)      full spectrum for columns j in [r*n1,(r+1)*n1), c < Hc
 //      fused |F|^2 / shell histogram (scatter_kernels.cuh, row remap) -> partial shell sums
 //   R  ncclAllReduce(sum) of the n_shells partial sums
+// Hc = number of columns c whose kv2[c] alone does not exceed the largest listed k^2: every k^2 of column c is
+// kv2[c] plus non-negative terms (whatever quirk Q1 pairs with it), so the other columns can never be binned and
+// are neither exchanged nor transformed along x -- exact, and it shrinks the exchange by Hc / H.
+// Overlap: chunk k's exchange runs on a second stream while the 2D FFT + pack of chunk k+1 run on the caller's
+// stream (the x chunks are independent until the 1D transform, which needs every plane and therefore follows the
+// last chunk).  With profiling on, the stages are serialised on the caller's stream so that each can be timed.
 //
 // NCCL is loaded with dlopen (the library the process already has -- torch's bundled
 // libnccl.so.2 -- or $SBX_NCCL_LIB), so libsimubox_b200.so has no link-time NCCL dependency.
@@ -91,14 +97,18 @@ int nccl_load() {
       return ::sbx::fail(SBX_ENCCL, "%s:%d %s -> %s", __FILE__, __LINE__, #call, g_nccl.GetErrorString(r_)); \
   } while (0)
 
-// X[x][j][c] -> Y[d][x][jl][c]: every (x, d) pair moves one contiguous run of n1*H elements.
+// F[xl][j][c < H] (one chunk of planes, xl local to the chunk) -> Y[d][x0 + xl][jl][c < Hc], j = d*n1 + jl:
+// every (xl, d) pair moves n1 rows of Hc elements.
 __global__ void __launch_bounds__(256)
-slab_pack_kernel(const double2* __restrict__ X, double2* __restrict__ Y, int n0, int P, long long run /* n1*H */) {
-  const int x = blockIdx.y / P, d = blockIdx.y - x * P;
-  const double2* src = X + ((long long)x * P + d) * run;
-  double2* dst = Y + ((long long)d * n0 + x) * run;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < run; i += (long long)gridDim.x * blockDim.x)
-    dst[i] = src[i];
+slab_pack_kernel(const double2* __restrict__ F, double2* __restrict__ Y, int n0, int x0, int P, int n1, int H, int Hc) {
+  const int xl = blockIdx.y / P, d = blockIdx.y - xl * P;
+  const long long run = (long long)n1 * Hc;
+  const double2* src = F + ((long long)xl * P + d) * n1 * H;
+  double2* dst = Y + ((long long)d * n0 + x0 + xl) * run;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < run; i += (long long)gridDim.x * blockDim.x) {
+    const long long jl = i / Hc;
+    dst[i] = src[jl * H + (i - jl * Hc)];
+  }
 }
 
 template <class T>
@@ -120,10 +130,15 @@ struct sbx_slab_plan {
   ShellDev shell{};
   std::vector<double> q_host;
   int n0 = 0, n1 = 0, H = 0;
-  long long blk = 0;  // elements exchanged per rank pair: n0*n1*H
+  int Hc = 0;         // columns c < Hc are exchanged and transformed along x
+  int K = 1, nc0 = 0; // chunks of the local planes and planes per chunk (n0 = K * nc0)
+  long long blk = 0;  // elements exchanged per rank pair: n0*n1*Hc
   cufftHandle fft2d = 0, fft1d = 0;
   bool have2d = false, have1d = false;
-  double2 *d_x = nullptr, *d_y = nullptr;
+  double2 *d_f = nullptr;                  // 2D spectrum of one chunk of planes: nc0 x N1 x H
+  double2 *d_x = nullptr, *d_y = nullptr;  // receive / send buffers: world x blk
+  cudaStream_t s_comm = nullptr;           // exchange stream
+  cudaEvent_t ev_chunk[16] = {}, ev_comm = nullptr;
   double *d_rep = nullptr, *d_kvlast = nullptr, *d_partial = nullptr;
   double2* d_plane2 = nullptr;
   int blocks = 1;
@@ -141,7 +156,10 @@ static void slab_free(sbx_slab_plan* p) {
   DeviceGuard guard(p->device);
   if (p->have2d) cufftDestroy(p->fft2d);
   if (p->have1d) cufftDestroy(p->fft1d);
-  cudaFree(p->d_x); cudaFree(p->d_y); cudaFree(p->d_rep); cudaFree(p->d_kvlast); cudaFree(p->d_partial);
+  cudaFree(p->d_f); cudaFree(p->d_x); cudaFree(p->d_y); cudaFree(p->d_rep); cudaFree(p->d_kvlast); cudaFree(p->d_partial);
+  if (p->s_comm) cudaStreamDestroy(p->s_comm);
+  for (cudaEvent_t e : p->ev_chunk) if (e) cudaEventDestroy(e);
+  if (p->ev_comm) cudaEventDestroy(p->ev_comm);
   cudaFree(p->d_plane2);
   cudaFree(p->d_modesum);
   if (p->inner) sbx_scatter_plan_destroy(p->inner);
@@ -169,7 +187,6 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
   p->n0 = (int)(N[0] / world);
   p->n1 = (int)(N[1] / world);
   p->H = (int)(N[2] / 2 + 1);
-  p->blk = (long long)p->n0 * p->n1 * p->H;
 
   // ---- mode: pruned DFT when every shell mode is a low one (the default cutoff = 30 case), else slab FFT.
   // SBX_SLAB_PATH=fft / pruned forces one of them.
@@ -221,7 +238,6 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
   g.N0 = (int)N[0]; g.N1 = (int)N[1]; g.N2 = (int)N[2];
   g.H = p->H;
   g.nreal = t.total();
-  g.nspec = (long long)N[0] * p->n1 * p->H;  // elements this rank bins
   g.factor = 1.0 / (double)g.nreal;
   g.n1loc = p->n1;
   g.joff = rank * p->n1;
@@ -253,12 +269,33 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
     slab_free(p);
     return fail(SBX_EINVAL, "%d shells exceed the shared-memory shell table", sh.n_shells);
   }
+  // columns worth exchanging: kv2 grows with c on 0..N2/2, and a column whose kv2[c] alone is beyond the table
+  // cannot hold a listed mode (SBX_SLAB_ALLCOLS=1 keeps all of them: the exchange-bound case for measurements)
+  p->Hc = 1;
+  while (p->Hc < p->H && t.kv[2][p->Hc] <= sh.vcut) ++p->Hc;
+  { const char* ac = getenv("SBX_SLAB_ALLCOLS"); if (ac && atoi(ac) == 1) p->Hc = p->H; }
+  p->blk = (long long)p->n0 * p->n1 * p->Hc;
+  g.Hs = p->Hc;
+  g.nspec = (long long)N[0] * p->n1 * p->Hc;  // elements this rank bins
+  // chunks of the local planes: the largest count <= SBX_SLAB_CHUNKS (default 4, at most 16) that divides n0
+  {
+    const char* ce = getenv("SBX_SLAB_CHUNKS");
+    int want = ce ? atoi(ce) : 4;
+    want = std::max(1, std::min(want, 16));
+    p->K = 1;
+    for (int k = want; k >= 1; --k) if (p->n0 % k == 0) { p->K = k; break; }
+    p->nc0 = p->n0 / p->K;
+  }
 
   const size_t spec_bytes = (size_t)world * p->blk * sizeof(double2);
-  cudaError_t e = cudaMalloc((void**)&p->d_x, spec_bytes);
+  cudaError_t e = cudaMalloc((void**)&p->d_f, (size_t)p->nc0 * N[1] * p->H * sizeof(double2));
+  if (e == cudaSuccess && world > 1) e = cudaMalloc((void**)&p->d_x, spec_bytes);
   if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_y, spec_bytes);
   if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_partial, (size_t)sh.n_shells * sizeof(double));
   for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&p->ev[i]);
+  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->s_comm, cudaStreamNonBlocking);
+  for (int i = 0; i < p->K && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&p->ev_chunk[i], cudaEventDisableTiming);
+  if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_comm, cudaEventDisableTiming);
   if (e != cudaSuccess) {
     slab_free(p);
     return fail(e == cudaErrorMemoryAllocation ? SBX_ENOMEM : SBX_ECUDA, "slab plan allocation: %s", cudaGetErrorString(e));
@@ -267,13 +304,13 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
     int n2[2] = {(int)N[1], (int)N[2]};
     size_t ws = 0;
     cufftResult r = cufftCreate(&p->fft2d);
-    if (r == CUFFT_SUCCESS) { p->have2d = true; r = cufftMakePlanMany(p->fft2d, 2, n2, nullptr, 1, 0, nullptr, 1, 0, CUFFT_D2Z, p->n0, &ws); }
+    if (r == CUFFT_SUCCESS) { p->have2d = true; r = cufftMakePlanMany(p->fft2d, 2, n2, nullptr, 1, 0, nullptr, 1, 0, CUFFT_D2Z, p->nc0, &ws); }
     if (r == CUFFT_SUCCESS) r = cufftCreate(&p->fft1d);
     if (r == CUFFT_SUCCESS) {
       p->have1d = true;
       int n1d[1] = {(int)N[0]};
       int embed[1] = {(int)N[0]};
-      const long long batch = (long long)p->n1 * p->H;
+      const long long batch = (long long)p->n1 * p->Hc;
       if (batch > 0x7fffffffLL) r = CUFFT_INVALID_SIZE;
       else r = cufftMakePlanMany(p->fft1d, 1, n1d, embed, (int)batch, 1, embed, (int)batch, 1, CUFFT_Z2Z, (int)batch, &ws);
     }
@@ -288,26 +325,46 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
   return SBX_OK;
 }
 
-// stage A: local planes -> packed send buffer d_y
-static int slab_stage_a(sbx_slab_plan* p, const double* local_slab, cudaStream_t st) {
+// stage A of chunk k: planes [k*nc0, (k+1)*nc0) of the local slab -> their part of the packed send buffer d_y
+static int slab_stage_a(sbx_slab_plan* p, const double* local_slab, int k, cudaStream_t st) {
+  const GridDev& g = p->grid;
   SBX_CUFFT(cufftSetStream(p->fft2d, st));
-  SBX_CUFFT(cufftExecD2Z(p->fft2d, const_cast<double*>(local_slab), (cufftDoubleComplex*)p->d_x));
-  if (p->world == 1) return SBX_OK;  // X already is [x][j][c]
-  const long long run = (long long)p->n1 * p->H;
-  dim3 grid((unsigned)std::min<long long>((run + 255) / 256, 64), (unsigned)(p->n0 * p->world));
-  slab_pack_kernel<<<grid, 256, 0, st>>>(p->d_x, p->d_y, p->n0, p->world, run);
+  SBX_CUFFT(cufftExecD2Z(p->fft2d, const_cast<double*>(local_slab) + (size_t)k * p->nc0 * g.N1 * g.N2, (cufftDoubleComplex*)p->d_f));
+  const long long run = (long long)p->n1 * p->Hc;
+  dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((run + 255) / 256, 64)), (unsigned)(p->nc0 * p->world));
+  slab_pack_kernel<<<grid, 256, 0, st>>>(p->d_f, p->d_y, p->n0, k * p->nc0, p->world, p->n1, p->H, p->Hc);
   SBX_CUDA(cudaGetLastError());
   return SBX_OK;
 }
 
-// stage B: received pencils d_x -> partial shell sums d_partial
+// the pencils stage B works on: the receive buffer, or the packed buffer itself when there is nothing to exchange
+static double2* slab_pencils(sbx_slab_plan* p) { return p->world > 1 ? p->d_x : p->d_y; }
+
+// exchange of chunk k (planes [k*nc0, (k+1)*nc0) of every slab): piece d of d_y goes to rank d, piece s of d_x
+// comes from rank s; the own piece is a device copy
+static int slab_exchange(sbx_slab_plan* p, int k, cudaStream_t st) {
+  const size_t piece = (size_t)p->nc0 * p->n1 * p->Hc, off = (size_t)k * piece;
+  SBX_NCCL(g_nccl.GroupStart());
+  for (int i = 1; i < p->world; ++i) {
+    const int to = (p->rank + i) % p->world, from = (p->rank - i + p->world) % p->world;
+    SBX_NCCL(g_nccl.Send(p->d_y + (size_t)to * p->blk + off, piece * 2, ncclDouble, to, p->comm, st));
+    SBX_NCCL(g_nccl.Recv(p->d_x + (size_t)from * p->blk + off, piece * 2, ncclDouble, from, p->comm, st));
+  }
+  SBX_NCCL(g_nccl.GroupEnd());
+  SBX_CUDA(cudaMemcpyAsync(p->d_x + (size_t)p->rank * p->blk + off, p->d_y + (size_t)p->rank * p->blk + off,
+                           piece * sizeof(double2), cudaMemcpyDeviceToDevice, st));
+  return SBX_OK;
+}
+
+// stage B: pencils -> partial shell sums d_partial
 static int slab_stage_b(sbx_slab_plan* p, cudaStream_t st) {
+  double2* pen = slab_pencils(p);
   SBX_CUFFT(cufftSetStream(p->fft1d, st));
-  SBX_CUFFT(cufftExecZ2Z(p->fft1d, (cufftDoubleComplex*)p->d_x, (cufftDoubleComplex*)p->d_x, CUFFT_FORWARD));
+  SBX_CUFFT(cufftExecZ2Z(p->fft1d, (cufftDoubleComplex*)pen, (cufftDoubleComplex*)pen, CUFFT_FORWARD));
   if (p->timed) cudaEventRecord(p->ev[3], st);
   const int ns = p->shell.n_shells;
   SBX_CUDA(cudaMemsetAsync(p->d_partial, 0, (size_t)ns * sizeof(double), st));
-  return launch_shell_histogram3(p->d_x, p->grid, p->shell, p->d_partial, p->blocks, st);
+  return launch_shell_histogram3(pen, p->grid, p->shell, p->d_partial, p->blocks, st);
 }
 
 // ------------------------------------------------------------------------------------ C ABI
@@ -384,19 +441,23 @@ extern "C" int sbx_scatter_slab_execute(sbx_slab_plan* p, const double* local_sl
     if (p->timed) cudaEventRecord(p->ev[4], st);
     return SBX_OK;
   }
-  if ((rc = slab_stage_a(p, local_slab, st))) return rc;
-  if (p->timed) cudaEventRecord(p->ev[1], st);
-  if (p->world > 1) {
-    // all-to-all: block d of d_y goes to rank d, block s of d_x comes from rank s
-    SBX_NCCL(g_nccl.GroupStart());
-    for (int k = 1; k < p->world; ++k) {
-      const int to = (p->rank + k) % p->world, from = (p->rank - k + p->world) % p->world;
-      SBX_NCCL(g_nccl.Send(p->d_y + (size_t)to * p->blk, (size_t)p->blk * 2, ncclDouble, to, p->comm, st));
-      SBX_NCCL(g_nccl.Recv(p->d_x + (size_t)from * p->blk, (size_t)p->blk * 2, ncclDouble, from, p->comm, st));
+  if (p->timed || p->world == 1) {
+    // serial form (stage timing; or nothing to exchange): all chunks through stage A, then all exchanges
+    for (int k = 0; k < p->K; ++k)
+      if ((rc = slab_stage_a(p, local_slab, k, st))) return rc;
+    if (p->timed) cudaEventRecord(p->ev[1], st);
+    for (int k = 0; k < p->K && p->world > 1; ++k)
+      if ((rc = slab_exchange(p, k, st))) return rc;
+  } else {
+    // pipelined form: the exchange of chunk k on s_comm overlaps stage A of chunk k + 1 on the caller's stream
+    for (int k = 0; k < p->K; ++k) {
+      if ((rc = slab_stage_a(p, local_slab, k, st))) return rc;
+      SBX_CUDA(cudaEventRecord(p->ev_chunk[k], st));
+      SBX_CUDA(cudaStreamWaitEvent(p->s_comm, p->ev_chunk[k], 0));
+      if ((rc = slab_exchange(p, k, p->s_comm))) return rc;
     }
-    SBX_NCCL(g_nccl.GroupEnd());
-    SBX_CUDA(cudaMemcpyAsync(p->d_x + (size_t)p->rank * p->blk, p->d_y + (size_t)p->rank * p->blk,
-                             (size_t)p->blk * sizeof(double2), cudaMemcpyDeviceToDevice, st));
+    SBX_CUDA(cudaEventRecord(p->ev_comm, p->s_comm));
+    SBX_CUDA(cudaStreamWaitEvent(st, p->ev_comm, 0));
   }
   if (p->timed) cudaEventRecord(p->ev[2], st);
   if ((rc = slab_stage_b(p, st))) return rc;
@@ -469,7 +530,8 @@ extern "C" int sbx_scatter_slab_emulate(int device, int world, const int64_t* N,
     if (!rc) cudaStreamSynchronize(st);
   } else if (!rc) {
     const long long slab = (long long)plans[0]->n0 * N[1] * N[2];
-    for (int r = 0; r < world && !rc; ++r) rc = slab_stage_a(plans[r], field + (size_t)r * slab, st);
+    for (int r = 0; r < world && !rc; ++r)
+      for (int k = 0; k < plans[r]->K && !rc; ++k) rc = slab_stage_a(plans[r], field + (size_t)r * slab, k, st);
     if (!rc && world > 1)
       for (int r = 0; r < world; ++r)      // receiver
         for (int s = 0; s < world; ++s) {  // sender

@@ -1075,13 +1075,16 @@ extern "C" int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* p, const double*
   }
   unsigned long long* stats = stats_host ? p->stats : nullptr;
   if (stats) SBX_CUDA(cudaMemsetAsync(stats, 0, 3 * sizeof(unsigned long long), st));
-  // Whole grids run the tile path (coarse -> mid -> label: 89 us at 256^3 / 4096 seeds); a plane range runs the cell
-  // path, which labels only the tiles of the range (the tile path would label the whole grid into scratch).
-  // SBX_VOR_PATH=cells|tiles forces one (read once).
+  // Path choice.  The tile path (coarse -> mid -> label) scans ALL S seeds once per 32^3 coarse tile, so its cost per
+  // voxel grows with S; the cell path's does not.  Measured on B200 (profiles/r02): 256^3 / 4096 seeds whole grid
+  // 89 us tiles vs 118 us cells; 512^3 / 32768 seeds 1.60 ms tiles vs 0.77 ms cells.  Whole grids therefore run the
+  // tile path up to 8192 seeds and the cell path beyond; a plane range always runs the cell path, which labels only
+  // the tiles of the range (the tile path would label the whole grid into scratch).  SBX_VOR_PATH=cells|tiles forces
+  // one (read once).
   static const int force = [] { const char* e = getenv("SBX_VOR_PATH"); return !e ? 0 : (e[0] == 'c' ? 1 : (e[0] == 't' ? 2 : 0)); }();
   const bool whole = x_lo == 0 && x_hi == N0;
   const bool cells = mode == 0 && !weights && (long long)S * (g.periodic ? 27 : 1) <= (1ll << 27) &&
-                     (force == 1 || (force == 0 && !whole));
+                     (force == 1 || (force == 0 && (!whole || S > 8192)));
   if (cells) {
     CellGeo c{};
     cell_geometry(p, g, S, (int)x_lo, (int)x_hi, c);

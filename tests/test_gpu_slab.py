@@ -40,6 +40,26 @@ def test_emulated_slab_matches_oracle(sbx_lib, monkeypatch, N, L, cutoff, world,
     check_scatter_rows(qI, ref, cutoff, last_shell_members(mat, L, cutoff, 1e-12))
 
 
+@pytest.mark.parametrize("chunks,allcols", [(1, 0), (3, 0), (8, 1), (16, 0), (2, 1)])
+@pytest.mark.parametrize("N,L,cutoff,world", [((32, 32, 32), (8.0, 8.0, 8.0), 400, 2), ((12, 8, 6), (2.0, 1.0, 1.5), 30, 4),
+                                              ((48, 16, 64), (3.0, 2.0, 5.0), 60, 2), ((16, 16, 16), (4.0, 4.0, 4.0), 5, 1)])
+def test_emulated_slab_fft_chunks_and_column_pruning(sbx_lib, monkeypatch, N, L, cutoff, world, chunks, allcols):
+    """Slab FFT mode with the local planes cut into 1 ... 16 chunks (the count is lowered to a divisor of the planes
+    per rank) and with / without the pruning of the exchanged columns (only c with kv2[c] <= the largest listed k^2
+    travel): the rows must not depend on either."""
+    from simubox_b200 import distributed as D
+
+    monkeypatch.setenv("SBX_SLAB_PATH", "fft")
+    monkeypatch.setenv("SBX_SLAB_CHUNKS", str(chunks))
+    monkeypatch.setenv("SBX_SLAB_ALLCOLS", str(allcols))
+    rng = np.random.default_rng(hash((N, world)) % 2 ** 32)
+    mat = rng.random(N)
+    I = D.slab_emulate(mat, L, world, cutoff=cutoff)
+    ref, _ = scatter_np.scattering_peak(mat, L, cutoff=cutoff)
+    plan = sbx_lib.ScatterPlan(N, L, cutoff, 1e-12, 1, sbx_lib.SBX_DEVICE_NONE)
+    check_scatter_rows(np.stack([plan.q, I], axis=1), ref, cutoff, last_shell_members(mat, L, cutoff, 1e-12))
+
+
 def test_emulated_slab_equals_single_gpu_plan(sbx_lib):
     import torch
 
@@ -80,16 +100,20 @@ def test_slab_rejects_bad_partition(sbx_lib):
     assert ei.value.code == -1
 
 
-@pytest.mark.parametrize("slab_path", ["fft", "pruned"])
-def test_nccl_slab_two_ranks(slab_path):
-    """The real NCCL path, one process per GPU: slab FFT (all-to-all + all-reduce) and pruned mode (all-reduce only)."""
+@pytest.mark.parametrize("slab_path,extra", [("fft", {}), ("pruned", {}), ("fft", {"SBX_SLAB_CHUNKS": "8", "SBX_SLAB_ALLCOLS": "1"}),
+                                             ("fft", {"SBX_SLAB_CHUNKS": "1"})])
+def test_nccl_slab_two_ranks(slab_path, extra):
+    """The real NCCL path, one process per GPU: slab FFT (chunked all-to-all on its own stream overlapping the 2D
+    transforms, + all-reduce; also with 8 chunks and every column exchanged, and unchunked) and pruned mode
+    (all-reduce only)."""
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs (the single-GPU emulation test covers the decomposition)")
     world = 2
+    port = 29517 + ["fft", "pruned"].index(slab_path) + 2 * len(extra)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
-           "--master-port", "29517" if slab_path == "fft" else "29518", str(ROOT / "tests" / "slab_worker.py"), "--grid", "64"]
-    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT), env=dict(os.environ, SBX_SLAB_PATH=slab_path))
+           "--master-port", str(port), str(ROOT / "tests" / "slab_worker.py"), "--grid", "64"]
+    res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT), env=dict(os.environ, SBX_SLAB_PATH=slab_path, **extra))
     assert res.returncode == 0, res.stdout[-3000:] + res.stderr[-3000:]
     assert "slab parity ok" in res.stdout
