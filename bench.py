@@ -276,7 +276,12 @@ def run_scatter(args):
     fused_ms_per_launch = fused_ms_per_step / max(own_per_step, 1)
     prof = {"transform_ms": transform_ms_per_step, "fused_ms": fused_ms_per_step, "own_launches": own_per_step}
 
-    # --- end to end through the host-buffer C-ABI call (pinned host memory)
+    # --- end to end through the host-buffer C-ABI call (pinned host memory).  The rank is bound to its GPU's NUMA-local
+    # CPUs BEFORE the pinned allocation, so that first touch places the staging buffer on that node.
+    from simubox_b200.distributed import bind_to_gpu_numa
+
+    affinity0 = os.sched_getaffinity(0)
+    numa = bind_to_gpu_numa(local)
     host = torch.empty((B, *shape), dtype=torch.float64, pin_memory=True)
     host.copy_(fields)
     torch.cuda.synchronize()
@@ -294,6 +299,7 @@ def run_scatter(args):
         step_host()
     torch.cuda.synchronize()
     e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / args.e2e_steps, world, dev)
+    os.sched_setaffinity(0, affinity0)  # the CPU-baseline leg below uses every core this process was given
     clk.__exit__()
     clocks = clk.summary()
     ns = plan.n_shells
@@ -362,7 +368,7 @@ def run_scatter(args):
                    "grid": [n, n, n], "fields_per_gpu": B, "path": pathname, "fields_per_launch": min(args.max_batch, B), "host_chunk": args.host_batch,
                    "l2": "inputs (4.3 GB per pass) exceed the 126 MB L2; no flush needed", "parallelism": f"fields sharded, {world} rank(s), no collective"},
         "e2e": {"value": B * world / (e2e_ms * 1e-3), "unit": "fields/s", "h2d_bytes_per_step": h2d, "d2h_bytes_per_step": d2h,
-                "ms_per_step": e2e_ms, "h2d_GBps": h2d / (e2e_ms * 1e-3) / 1e9, "api": "Scatter.sacttering_peak_batch(pinned host tensor) -> sbx_scatter_execute_host"},
+                "ms_per_step": e2e_ms, "h2d_GBps": h2d / (e2e_ms * 1e-3) / 1e9, "numa_binding_rank0": numa, "api": "Scatter.sacttering_peak_batch(pinned host tensor) -> sbx_scatter_execute_host"},
         "gpu_launches": int(round(own_per_step * args.steps)),
         "roofline": roof,
         "cpu_baseline": {"value": cpu_rate, "unit": "fields/s", "cores": cores, "kind": "port", "txyz": "vectorised",

@@ -279,3 +279,43 @@ def slab_emulate(field, L, world: int, cutoff: int = 30, threshold: float = 1e-1
                                                    stream_ptr(device)))
     plan.close()
     return out.cpu().numpy()
+
+
+def gpu_numa_cpus(device: int):
+    """CPUs local to ``cuda:device`` according to sysfs (``/sys/bus/pci/devices/<bus id>/local_cpulist``), with the NUMA
+    node (-1 = the platform reports none).  Returns (sorted cpu list, node) or ([], -1) when sysfs has no answer."""
+    import torch
+
+    try:
+        prop = torch.cuda.get_device_properties(device)
+        bus = f"{getattr(prop, 'pci_domain_id', 0):04x}:{prop.pci_bus_id:02x}:{prop.pci_device_id:02x}.0"
+        base = f"/sys/bus/pci/devices/{bus}"
+        with open(f"{base}/local_cpulist") as fh:
+            text = fh.read().strip()
+        try:
+            with open(f"{base}/numa_node") as fh:
+                node = int(fh.read().strip())
+        except Exception:
+            node = -1
+        cpus = []
+        for part in filter(None, text.split(",")):
+            a, _, b = part.partition("-")
+            cpus.extend(range(int(a), int(b or a) + 1))
+        return sorted(cpus), node
+    except Exception:
+        return [], -1
+
+
+def bind_to_gpu_numa(device: int) -> dict:
+    """Pin this process to the CPUs local to its GPU BEFORE it allocates pinned host memory (first touch then places
+    the staging buffers on the GPU's NUMA node).  No-op when sysfs gives no list or the list does not intersect the
+    CPUs the process may use.  Returns what was done, for the bench record."""
+    cpus, node = gpu_numa_cpus(device)
+    allowed = os.sched_getaffinity(0)
+    use = sorted(set(cpus) & allowed)
+    info = {"numa_node": node, "local_cpus": len(cpus), "allowed_cpus": len(allowed), "bound": False}
+    if use and len(use) < len(allowed):
+        os.sched_setaffinity(0, use)
+        info["bound"] = True
+        info["bound_cpus"] = len(use)
+    return info
