@@ -2,7 +2,7 @@
 
 Follows ``/root/reference/SimuBox/calculator/scatter.py`` operation by operation
 (numpy/scipy, fp64).  Pinned against the live reference by ``oracle/make_golden.py``
-and ``tests/test_oracle_vs_reference.py``; fixtures in ``tests/golden/``.
+and ``tests/test_oracle_golden.py`` (every golden, plus the live reference when present); fixtures in ``tests/golden/``.
 
 Two restatements are kept side by side:
 

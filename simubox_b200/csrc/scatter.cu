@@ -101,6 +101,9 @@ struct sbx_scatter_plan {
   int n_umodes = 0;
   bool pruned_ok = false;
   // fused single-kernel variant (pruned_fused.cuh)
+  // debugging switches, read ONCE at plan creation (SBX_BULK=0: LDG row-blocked kernel instead of the bulk-staged one;
+  // SBX_FUSED_BLOCKED=1: row-blocked kernels on grids that would run the whole-plane kernels)
+  bool env_bulk_off = false, env_force_blocked = false;
   bool fused_ok = false;    // whole planes fit the shared-memory scheme of pruned_fused_kernel / pruned_ring_kernel
   bool modes_ok = false;    // every listed mode lies in the 8 x 8 (k_y, k_z) tile: tables below are built
   bool blocked_ok = false;  // pruned_blocked_kernel applies (any N1 = yb_rows * yblocks)
@@ -408,6 +411,8 @@ extern "C" int sbx_scatter_plan_create_ex(sbx_scatter_plan** out, int device, in
   if (!p) return fail(SBX_ENOMEM, "out of host memory");
   p->device = device;
   p->max_batch = max_batch;
+  { const char* e = getenv("SBX_BULK"); p->env_bulk_off = e && atoi(e) == 0; }
+  { const char* e = getenv("SBX_FUSED_BLOCKED"); p->env_force_blocked = e && atoi(e) != 0; }
   if ((rc = build_shell_table(p->tab, ndim, N, L, cutoff, threshold))) { free_plan(p); return rc; }
   fill_q(p);
   if ((rc = build_device_tables(p))) { free_plan(p); return rc; }
@@ -558,10 +563,9 @@ namespace sbx { static int blocked_unit_planes(const sbx_scatter_plan* p, bool b
 // The bulk-staged form of the blocked kernel (pruned_bulk_kernel) applies when rows split into 512-byte pieces per
 // half (N2 % 128 == 0), a block of rows gives every warp whole row groups (yb_rows % 64 == 0) and the stages, the z
 // twiddles and the work area fit one CTA's shared memory.  Measured on B200 (profiles/r01): see DESIGN.md section 3.
-// SBX_BULK=0 keeps the LDG blocked kernel (read per call: the tests switch it).
+// SBX_BULK=0 at plan creation keeps the LDG blocked kernel.
 static bool bulk_applies(const sbx_scatter_plan* p, size_t bwork) {
-  const char* e = getenv("SBX_BULK");
-  if (e && atoi(e) == 0) return false;
+  if (p->env_bulk_off) return false;
   const bool two_items = (p->yb_rows / 64) * (p->grid.N2 / 128) >= 2 || p->fused_xc >= 2;  // per warp and unit
   return p->grid.N2 % 128 == 0 && p->yb_rows % 64 == 0 && two_items && bulk_smem_bytes(p->grid.N2, bwork) <= kMaxTmaSmem;
 }
@@ -591,8 +595,7 @@ static int run_scatter(sbx_scatter_plan* p, const double* fields, int batch, dou
     A.partial = p->d_partial; A.ctrl = p->d_ctrl;
     A.do_peaks = do_peaks ? 1 : 0; A.q = p->d_q; A.pp = pp;
     A.parts = A.chunks; A.planes = g.N0; A.x_base = 0; A.yb_rows = g.N1; A.yblocks = 1; A.finish = 1;
-    const char* fb_env = getenv("SBX_FUSED_BLOCKED");  // read per call: the tests switch it
-    const int force_blocked = fb_env ? atoi(fb_env) : 0;
+    const int force_blocked = p->env_force_blocked ? 1 : 0;
     // whole-plane kernels need >= 2 CTAs per SM to hide their barriers; beyond that (512^3, 1024^3): row-blocked kernel
     const bool whole_plane_thin = fused_smem_bytes(g.N0, g.N1, g.N2, fused_work_doubles(g.N1, ns, p->n_umodes, do_peaks ? pp.step : 0, do_peaks)) > 113 * 1024;
     if ((!p->fused_ok || force_blocked || whole_plane_thin) && p->blocked_ok) {

@@ -3,7 +3,7 @@
 Mirrors ``SimuBox/toolkit/reader.py``: ``read_printout`` (:43-75), ``read_density`` (:78-230,
 text and binary layouts) and ``parse_density`` (:345-415, target / permute / slices / periodic
 ``expand``).  Argument names, defaults, return models and error behaviour follow the
-reference; the body is new (numpy's C text parser instead of the pandas python engine).
+reference; the body is new (the native multithreaded parser csrc/text_table.cpp instead of the pandas python engine).
 
 File formats:
   text   line 0 = ``Nx Ny Nz`` ints (left-padded with 1s to 3 entries), optional line 1 =
@@ -76,9 +76,12 @@ def _file_bytes(path: Path) -> np.ndarray:
 
 def _load_text_table(raw: np.ndarray, skip: int, threads: int = 0) -> np.ndarray:
     """Blank-separated numeric rows -> (rows, ncol) fp64 through the native multithreaded parser
-    (csrc/text_table.cpp: correctly rounded conversion = the doubles Python's float() gives the
-    reference's pandas python-engine parse, reader.py:170-172).  ValueError on ragged or
-    non-numeric rows, like the reference's parse."""
+    (csrc/text_table.cpp restates pandas' ``precise_xstrtod``, the conversion behind the reference's
+    ``pd.read_csv(..., engine="python")``, reader.py:170-172: the doubles are the reference's bit for bit, which beyond
+    15 significant digits can be one ulp from the correctly rounded value ``float()`` would give).  ValueError on
+    non-numeric or ragged rows.  One divergence: a row SHORTER than the first makes pandas NaN-pad without an error,
+    here it raises and so takes the reference's header-guess retry (reader.py:173-186) -- benign for well-formed
+    files, which is all the reference's writers produce."""
     import ctypes as C
 
     from . import _lib

@@ -199,8 +199,10 @@ def test_blocked_pruned_kernel_vs_gather(sbx_lib, torch_cuda, monkeypatch, shape
     N2 % 128 == 0 and blocks of 64 k rows run the bulk-staged kernel (TMA pieces of 1, 2 or 3 segments per half row);
     it keeps the summation order of the LDG blocked kernel, so the two must agree bit for bit."""
     from simubox_b200 import Scatter
+    from simubox_b200.scatter import clear_plans
 
-    monkeypatch.setenv("SBX_FUSED_BLOCKED", "1")
+    monkeypatch.setenv("SBX_FUSED_BLOCKED", "1")  # the switches are read when a plan is created: drop the cached ones
+    clear_plans()
     rng = np.random.default_rng(sum(shape))
     mats = [rng.random(shape) for _ in range(2)]
     L = (6.0, 6.0, 6.0)
@@ -212,11 +214,13 @@ def test_blocked_pruned_kernel_vs_gather(sbx_lib, torch_cuda, monkeypatch, shape
     assert get_plan(shape, L, 30, 1e-12, max_batch=2, path=FUSED).kernel == ("pruned_bulk_kernel" if bulk else "pruned_blocked_kernel")
     if bulk:
         monkeypatch.setenv("SBX_BULK", "0")
+        clear_plans()
         ldg = run_scatter(sbx_lib, torch_cuda, mats, L, 30, 1e-12, FUSED, peaks=pk)
         assert get_plan(shape, L, 30, 1e-12, max_batch=2, path=FUSED).kernel == "pruned_blocked_kernel"
         monkeypatch.delenv("SBX_BULK")
         assert np.array_equal(out["I"].cpu().numpy(), ldg["I"].cpu().numpy())
     monkeypatch.delenv("SBX_FUSED_BLOCKED")
+    clear_plans()
     ref = run_scatter(sbx_lib, torch_cuda, mats, L, 30, 1e-12, GATHER, peaks=pk)
     a, b = out["I"].cpu().numpy(), ref["I"].cpu().numpy()
     assert np.all(np.abs(a[:, :-1] - b[:, :-1]) <= 1e-9 * np.abs(b[:, :-1]) + 1e-12 * np.abs(b).max())
