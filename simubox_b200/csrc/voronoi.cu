@@ -1075,16 +1075,21 @@ extern "C" int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* p, const double*
   }
   unsigned long long* stats = stats_host ? p->stats : nullptr;
   if (stats) SBX_CUDA(cudaMemsetAsync(stats, 0, 3 * sizeof(unsigned long long), st));
-  // Path choice.  The tile path (coarse -> mid -> label) scans ALL S seeds once per 32^3 coarse tile, so its cost per
-  // voxel grows with S; the cell path's does not.  Measured on B200 (profiles/r02): 256^3 / 4096 seeds whole grid
-  // 89 us tiles vs 118 us cells; 512^3 / 32768 seeds 1.60 ms tiles vs 0.77 ms cells.  Whole grids therefore run the
-  // tile path up to 8192 seeds and the cell path beyond; a plane range always runs the cell path, which labels only
-  // the tiles of the range (the tile path would label the whole grid into scratch).  SBX_VOR_PATH=cells|tiles forces
-  // one (read once).
+  // Path choice, from the measured sweep profiles/r02/voronoi_paths.jsonl (whole grids, B200; tiles vs cells):
+  //   spacing h = (voxels / S)^(1/d)   256^3: h 32  75 vs  97 us | h 16  91 vs 122 us | h 10.7  187 vs 182 us | h 8  1.8 s vs 0.88 ms
+  //                                    512^3: h 32 0.52 vs 0.58 ms | h 16 (32768 seeds) 1.58 vs 0.76 ms;  128^3 h 8: 39.9 vs 0.069 ms
+  // The tile path stages at most kCap = 128 candidates per 16^3 mid tile and falls back to a full scan beyond (dense
+  // seeds: catastrophic), and its coarse kernel scans ALL S seeds once per 32^3 tile (S / 32768 tests per voxel);
+  // the cell path has neither limit but a higher fixed cost.  So: whole grids run the tile path when the seeds are
+  // sparse (h >= 11 voxels) and few (S < 12000), the cell path otherwise; a plane range always runs the cell path,
+  // which labels only the tiles of the range.  SBX_VOR_PATH=cells|tiles forces one (read once).
   static const int force = [] { const char* e = getenv("SBX_VOR_PATH"); return !e ? 0 : (e[0] == 'c' ? 1 : (e[0] == 't' ? 2 : 0)); }();
   const bool whole = x_lo == 0 && x_hi == N0;
+  double vox = 1.0;
+  for (int a = off; a < 3; ++a) vox *= (double)g.N[a];
+  const double spacing = pow(vox / (double)S, 1.0 / p->ndim);
   const bool cells = mode == 0 && !weights && (long long)S * (g.periodic ? 27 : 1) <= (1ll << 27) &&
-                     (force == 1 || (force == 0 && (!whole || S > 8192)));
+                     (force == 1 || (force == 0 && (!whole || S >= 12000 || spacing < 11.0)));
   if (cells) {
     CellGeo c{};
     cell_geometry(p, g, S, (int)x_lo, (int)x_hi, c);

@@ -406,25 +406,32 @@ __device__ __forceinline__ void label_tile(const CellGeo& g, const int t[3], con
           const int srow = __shfl_sync(kFull, s, pos), orow = __shfl_sync(kFull, off, pos);
           unsigned key = 0xffffffffu;
           float need = 0.f;
+          bool inside = false;
+          SeedRec v;
           if (j < tot) {
-            const SeedRec v = ld_rec(pts + srow + (j - orow));
+            v = ld_rec(pts + srow + (j - orow));
             const double ax = ND == 3 ? fabs(v.x - c[0]) : 0.0, ay = fabs(v.y - c[1]), az = fabs(v.z - c[2]);
             key = (__float_as_uint((float)(ax * ax + ay * ay + az * az)) & ~31u) | (unsigned)lane;
             // farthest voxel of the tile from this point, rounded up: what the search box has to cover if it becomes A
             const float fx = (float)(ax + hh[0]), fy = (float)(ay + hh[1]), fz = (float)(az + hh[2]);
             need = sqrtf(fx * fx + fy * fy + fz * fz) * 1.0001f + 1e-3f;
-            const int slot = n + j;
-            if (slot < kStage) s_stage[slot] = v;
+            // the cells of the search box overhang it: a point farther than R from the tile's box on some axis is
+            // farther than R from every voxel of the tile and is not staged (when the box is the whole cell grid
+            // there is no R to trust and everything is kept)
+            inside = all || (ax <= hh[0] + R && ay <= hh[1] + R && az <= hh[2] + R);
           }
+          const unsigned bal = __ballot_sync(kFull, inside);
+          const int slot = n + __popc(bal & lt);
+          if (inside && slot < kStage) s_stage[slot] = v;
           const unsigned kmin = __reduce_min_sync(kFull, key);
           if (kmin < bkey) {  // uniform
             bkey = kmin;
             const int src = kmin & 31u;
             bneed = __shfl_sync(kFull, need, src);
-            slotA = n + j0 + src;
+            slotA = __shfl_sync(kFull, inside ? slot : -1, src);  // -1: outside the box, then bneed > R and the search repeats
           }
+          n += __popc(bal);
         }
-        n += tot;
       }
       if (bkey == 0xffffffffu) {  // no point in the box yet
         if (all) break;  // cannot happen: S >= 1 and every seed keeps an image
