@@ -516,7 +516,7 @@ def _slab_mode(args, mode, local_slab, ctx, env=None):
     prof = {k: float(np.mean([st[k] for st in stages])) for k in stages[0]}
     prof = {k: max_over_ranks(v, world, dev) for k, v in prof.items()}
     I = out.cpu().numpy()
-    rec = {"path": "pruned_dft" if slab.path == 4 else "slab_fft", "ms_per_step": ms, "stage_ms": prof, "kernel": slab.kernel,
+    rec = {"path": "pruned_dft" if slab.path == 4 else "slab_fft", "exchange": slab.exchange, "ms_per_step": ms, "stage_ms": prof, "kernel": slab.kernel,
            "n_shells": int(slab.n_shells), "clocks": clk.summary()}
     q = slab.q.copy()
     slab.close()
@@ -548,11 +548,13 @@ def run_slab(args, modes=("pruned", "fft")):
     for mode in modes:
         recs[mode], rows[mode], q = _slab_mode(args, mode, local_slab, ctx)
     if "fft" in modes and world > 1:
-        # the exchange-bound form of the same mode: every column of the half spectrum travels (what a cutoff that
-        # reaches the Nyquist column needs), with the chunked exchange overlapped (default) and unchunked
-        recs["fft_allcols"], rows["fft_allcols"], q = _slab_mode(args, "fft", local_slab, ctx, {"SBX_SLAB_ALLCOLS": "1"})
-        recs["fft_allcols_unchunked"], rows["fft_allcols_unchunked"], q = _slab_mode(args, "fft", local_slab, ctx, {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_CHUNKS": "1"})
-        recs["fft_allcols_chunks8"], rows["fft_allcols_chunks8"], q = _slab_mode(args, "fft", local_slab, ctx, {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_CHUNKS": "8"})
+        # "fft" above runs the default exchange (fused pack + push into the peers' buffers over NVLink when CUDA IPC maps
+        # them, else NCCL send/recv).  Variants: the exchange-bound form of the mode, where every column of the half
+        # spectrum travels (what a cutoff reaching the Nyquist column needs): fused / NCCL chunked / NCCL unchunked.
+        for name, env in (("fft_allcols", {"SBX_SLAB_ALLCOLS": "1"}),
+                          ("fft_allcols_nccl", {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_EXCHANGE": "nccl"}),
+                          ("fft_allcols_nccl_unchunked", {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_EXCHANGE": "nccl", "SBX_SLAB_CHUNKS": "1"})):
+            recs[name], rows[name], q = _slab_mode(args, "fft", local_slab, ctx, env)
     del local_slab
     torch.cuda.empty_cache()
     if rank != 0:
@@ -573,24 +575,29 @@ def run_slab(args, modes=("pruned", "fft")):
         rec["roofline"] = {"bound": "hbm", "kernel": (rec["kernel"] or "pruned_blocked_kernel") if pruned else "cuFFT 2D + slab_pack_kernel + cuFFT 1D + shell_histogram_kernel",
                            "achieved": bytes_field / world / (rec["ms_per_step"] * 1e-3) / 1e9, "unit": "GB/s",
                            "frac": bytes_field / world / (rec["ms_per_step"] * 1e-3) / 1e9 / peak, "algorithmic_bytes_per_field": bytes_field}
-        rec["parallelism"] = ("all-reduce of the mode sums (no all-to-all)" if pruned else "NCCL all-to-all (send/recv group) + all-reduce")
+        rec["parallelism"] = ("all-reduce of the mode sums (no all-to-all)" if pruned else
+                              ("pack kernel stores into the peers' buffers over NVLink (CUDA IPC) + 4-byte barrier all-reduce + all-reduce of the shell sums"
+                               if rec.get("exchange") == "p2p_fused" else "NCCL all-to-all (send/recv group) + all-reduce"))
         if not pruned and world > 1 and rec["stage_ms"].get("all_to_all_ms"):
             allc = mode.startswith("fft_allcols")
             rec["columns_exchanged"] = "all (N2/2+1)" if allc else "only c with kv2[c] <= largest listed k^2"
-            if allc:
+            if rec.get("exchange") == "p2p_fused":
+                rec["stage_note"] = "fused exchange: the transfer is inside stage A (pack kernel stores into the peers); 'all_to_all_ms' is the 4-byte arrival barrier"
+            elif allc:
                 sent = spec / world * (world - 1) / world  # bytes each GPU sends (and receives)
                 rec["all_to_all_GBps_per_gpu"] = sent / (rec["stage_ms"]["all_to_all_ms"] * 1e-3) / 1e9
             # stage_ms comes from serialised (profiled) steps; ms_per_step from the pipelined ones
             serial = sum(rec["stage_ms"].values())
             rec["serial_stage_sum_ms"] = serial
-            rec["all_to_all_hidden_frac"] = max(0.0, min(1.0, (serial - rec["ms_per_step"]) / rec["stage_ms"]["all_to_all_ms"]))
+            if rec.get("exchange") != "p2p_fused":
+                rec["all_to_all_hidden_frac"] = max(0.0, min(1.0, (serial - rec["ms_per_step"]) / rec["stage_ms"]["all_to_all_ms"]))
     if "pruned" in rows and "fft" in rows:
         a, b = rows["pruned"], rows["fft"]
         full = len(a) - 1
         tol = 1e-9 * np.abs(a[:full]) + 1e-12 * np.abs(a[1:]).max()
         out["slab_parity"] = bool(np.all(np.abs(a[:full] - b[:full]) <= tol))
         out["slab_parity_worst_rel"] = float(np.max(np.abs(a[:full] - b[:full]) / np.maximum(np.abs(a[:full]), 1e-300)))
-        for extra in ("fft_allcols", "fft_allcols_unchunked", "fft_allcols_chunks8"):
+        for extra in ("fft_allcols", "fft_allcols_nccl", "fft_allcols_nccl_unchunked"):
             if extra in rows:
                 out["slab_parity"] = bool(out["slab_parity"] and np.all(np.abs(a[:full] - rows[extra][:full]) <= tol))
     first = recs[modes[0]]

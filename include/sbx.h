@@ -198,6 +198,20 @@ int sbx_scatter_slab_shells(const sbx_slab_plan* plan, int* n_shells, double* q_
                             int64_t* count_host);
 int sbx_scatter_slab_execute(sbx_slab_plan* plan, const double* local_slab, double* shell_I,
                              void* stream);
+/* Fused pack + exchange over peer memory for the slab FFT mode (no counterpart in the reference: it has no
+ * multi-GPU path; the exchange it stands for is the FFTW-MPI transpose of work/.../abc_star_short.c:270-286).
+ * After plan creation every rank exports the CUDA IPC handle of its receive buffer, the SBX_IPC_HANDLE_BYTES-byte
+ * handles of all ranks are gathered by any means (rank order) and attached on every rank; from then on
+ * sbx_scatter_slab_execute packs each destination's piece straight into that rank's buffer over NVLink (one kernel,
+ * no ncclSend/ncclRecv; a 4-byte all-reduce is the arrival barrier).  Ranks must be processes on one node with
+ * peer access (NVLink / NVSwitch); up to 16 ranks.  A plan in pruned mode ignores both calls.  Before destroying the
+ * plans: detach on every rank, then a barrier of the caller's, then destroy (the exporter must outlive the mappings).
+ * sbx_scatter_slab_exchange: 0 = none (pruned mode), 1 = NCCL send/recv, 2 = fused peer stores. */
+#define SBX_IPC_HANDLE_BYTES 64
+int sbx_scatter_slab_ipc_export(sbx_slab_plan* plan, void* handle_host /* SBX_IPC_HANDLE_BYTES */);
+int sbx_scatter_slab_ipc_attach(sbx_slab_plan* plan, const void* handles_host /* world x SBX_IPC_HANDLE_BYTES */);
+int sbx_scatter_slab_ipc_detach(sbx_slab_plan* plan);
+int sbx_scatter_slab_exchange(const sbx_slab_plan* plan);
 /* stage timing of the last execute after set_profiling(1): ms4_host = [2D FFT + pack, all-to-all,
  * 1D FFT, histogram + all-reduce]; synchronises on the last event */
 /* SBX_SCATTER_PRUNED_FUSED when the plan runs the pruned DFT (every shell mode low: each rank reduces its planes

@@ -14,7 +14,7 @@ for k in ("voronoi","voronoi_sharded","slab","sweep"):
     if "error" in v: print(k, "ERROR", v["error"]); continue
     if k=="slab":
         print(k, "parity", v.get("slab_parity"), v.get("slab_parity_worst_rel"), "leg", v.get("leg_seconds"))
-        for m,r in v["modes"].items(): print("   ", m, r["path"], round(r["ms_per_step"],3), {k:round(x,3) for k,x in r["stage_ms"].items()}, "a2a GB/s", r.get("all_to_all_GBps_per_gpu"), "hidden", r.get("all_to_all_hidden_frac"), "frac", round(r["roofline"]["frac"],3))
+        for m,r in v["modes"].items(): print("   ", m, r.get("exchange"), round(r["ms_per_step"],3), {k:round(x,3) for k,x in r["stage_ms"].items()}, "a2a GB/s", r.get("all_to_all_GBps_per_gpu"), "hidden", r.get("all_to_all_hidden_frac"), "frac", round(r["roofline"]["frac"],3))
     elif k=="voronoi_sharded":
         for g in v["grids"]: print(k, g)
     else: print(k, v.get("value"), v.get("ms_per_step"), "leg", v.get("leg_seconds"))

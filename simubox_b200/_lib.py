@@ -58,6 +58,10 @@ _SIGNATURES = {
     "sbx_scatter_slab_shells": (C.c_int, [_vp, C.POINTER(C.c_int), _f64p, _i64p]),
     "sbx_scatter_slab_execute": (C.c_int, [_vp, _vp, _vp, _vp]),
     "sbx_scatter_slab_plan_destroy": (C.c_int, [_vp]),
+    "sbx_scatter_slab_ipc_export": (C.c_int, [_vp, _vp]),
+    "sbx_scatter_slab_ipc_attach": (C.c_int, [_vp, _vp]),
+    "sbx_scatter_slab_ipc_detach": (C.c_int, [_vp]),
+    "sbx_scatter_slab_exchange": (C.c_int, [_vp]),
     "sbx_scatter_slab_set_profiling": (C.c_int, [_vp, C.c_int]),
     "sbx_scatter_slab_profile": (C.c_int, [_vp, _f64p]),
     "sbx_scatter_slab_emulate": (C.c_int, [C.c_int, C.c_int, _i64p, _f64p, C.c_int, C.c_double, _vp, _vp, _vp]),

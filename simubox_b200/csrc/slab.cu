@@ -19,6 +19,14 @@
 // stream (the x chunks are independent until the 1D transform, which needs every plane and therefore follows the
 // last chunk).  With profiling on, the stages are serialised on the caller's stream so that each can be timed.
 //
+// Fused pack + exchange (r02, sbx_scatter_slab_ipc_export / _attach): once the ranks have mapped each other's receive
+// buffers with CUDA IPC, the pack kernel stores every destination's piece STRAIGHT INTO THAT PEER'S d_x over NVLink
+// (slab_push_kernel: one kernel packs and exchanges, tile by tile, no send buffer, no ncclSend/ncclRecv); chunk k is
+// pushed on the second stream while chunk k + 1 is transformed (two chunk buffers).  What is left for NCCL is a
+// 4-byte all-reduce as the "every piece has landed" barrier before the 1D transform.  No barrier is needed before
+// the pushes: every execute ends with the all-reduce of the shell sums, which no rank passes before all ranks have
+// finished reading their d_x.
+//
 // NCCL is loaded with dlopen (the library the process already has -- torch's bundled
 // libnccl.so.2 -- or $SBX_NCCL_LIB), so libsimubox_b200.so has no link-time NCCL dependency.
 // sbx_scatter_slab_emulate runs the same stages for all P ranks on ONE device with device
@@ -111,6 +119,22 @@ slab_pack_kernel(const double2* __restrict__ F, double2* __restrict__ Y, int n0,
   }
 }
 
+// Fused pack + exchange: like slab_pack_kernel, but piece d goes straight into rank d's receive buffer
+// X_d[(sender*n0 + x0 + xl)][jl][c < Hc] (peer memory mapped through CUDA IPC; the own piece is local).
+struct PeerPtrs { double2* x[16]; };
+__global__ void __launch_bounds__(256)
+slab_push_kernel(const double2* __restrict__ F, PeerPtrs peers, int sender, int n0, int x0, int P, int n1, int H, int Hc) {
+  const int xl = blockIdx.y / P, d = blockIdx.y - xl * P;
+  const long long run = (long long)n1 * Hc;
+  const double2* src = F + ((long long)xl * P + d) * n1 * H;
+  double2* dst = peers.x[d] + ((long long)sender * n0 + x0 + xl) * run;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < run; i += (long long)gridDim.x * blockDim.x) {
+    const long long jl = i / Hc;
+    dst[i] = src[jl * H + (i - jl * Hc)];
+  }
+  __threadfence_system();  // the stores to peer memory are performed before the kernel counts as complete
+}
+
 template <class T>
 int upload(T** dptr, const std::vector<T>& h) {
   *dptr = nullptr;
@@ -139,6 +163,13 @@ struct sbx_slab_plan {
   double2 *d_x = nullptr, *d_y = nullptr;  // receive / send buffers: world x blk
   cudaStream_t s_comm = nullptr;           // exchange stream
   cudaEvent_t ev_chunk[16] = {}, ev_comm = nullptr;
+  // fused pack + exchange over peer memory (after sbx_scatter_slab_ipc_attach)
+  bool p2p = false;
+  double2* d_f2 = nullptr;                 // second chunk buffer (chunk k + 1 is transformed while chunk k is pushed)
+  double2* peer_x[16] = {};                // receive buffers of all ranks (own: d_x), IPC-mapped
+  bool peer_open[16] = {};
+  cudaEvent_t ev_push[16] = {};
+  int* d_flag = nullptr;                   // operand of the barrier all-reduce
   double *d_rep = nullptr, *d_kvlast = nullptr, *d_partial = nullptr;
   double2* d_plane2 = nullptr;
   int blocks = 1;
@@ -157,6 +188,9 @@ static void slab_free(sbx_slab_plan* p) {
   if (p->have2d) cufftDestroy(p->fft2d);
   if (p->have1d) cufftDestroy(p->fft1d);
   cudaFree(p->d_f); cudaFree(p->d_x); cudaFree(p->d_y); cudaFree(p->d_rep); cudaFree(p->d_kvlast); cudaFree(p->d_partial);
+  for (int r = 0; r < 16; ++r) if (p->peer_open[r]) cudaIpcCloseMemHandle(p->peer_x[r]);
+  cudaFree(p->d_f2); cudaFree(p->d_flag);
+  for (cudaEvent_t e : p->ev_push) if (e) cudaEventDestroy(e);
   if (p->s_comm) cudaStreamDestroy(p->s_comm);
   for (cudaEvent_t e : p->ev_chunk) if (e) cudaEventDestroy(e);
   if (p->ev_comm) cudaEventDestroy(p->ev_comm);
@@ -296,6 +330,12 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
   if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->s_comm, cudaStreamNonBlocking);
   for (int i = 0; i < p->K && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&p->ev_chunk[i], cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_comm, cudaEventDisableTiming);
+  if (e == cudaSuccess && world > 1 && world <= 16) {
+    e = cudaMalloc((void**)&p->d_f2, (size_t)p->nc0 * N[1] * p->H * sizeof(double2));
+    if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_flag, sizeof(int));
+    if (e == cudaSuccess) e = cudaMemset(p->d_flag, 0, sizeof(int));
+    for (int i = 0; i < p->K && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&p->ev_push[i], cudaEventDisableTiming);
+  }
   if (e != cudaSuccess) {
     slab_free(p);
     return fail(e == cudaErrorMemoryAllocation ? SBX_ENOMEM : SBX_ECUDA, "slab plan allocation: %s", cudaGetErrorString(e));
@@ -333,6 +373,23 @@ static int slab_stage_a(sbx_slab_plan* p, const double* local_slab, int k, cudaS
   const long long run = (long long)p->n1 * p->Hc;
   dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((run + 255) / 256, 64)), (unsigned)(p->nc0 * p->world));
   slab_pack_kernel<<<grid, 256, 0, st>>>(p->d_f, p->d_y, p->n0, k * p->nc0, p->world, p->n1, p->H, p->Hc);
+  SBX_CUDA(cudaGetLastError());
+  return SBX_OK;
+}
+
+// stage A of chunk k in the fused form: transform into chunk buffer `buf`; slab_push then packs it into the peers
+static int slab_fft_chunk(sbx_slab_plan* p, const double* local_slab, int k, double2* buf, cudaStream_t st) {
+  const GridDev& g = p->grid;
+  SBX_CUFFT(cufftSetStream(p->fft2d, st));
+  SBX_CUFFT(cufftExecD2Z(p->fft2d, const_cast<double*>(local_slab) + (size_t)k * p->nc0 * g.N1 * g.N2, (cufftDoubleComplex*)buf));
+  return SBX_OK;
+}
+static int slab_push(sbx_slab_plan* p, int k, const double2* buf, cudaStream_t st) {
+  PeerPtrs pp;
+  for (int r = 0; r < 16; ++r) pp.x[r] = r < p->world ? p->peer_x[r] : nullptr;
+  const long long run = (long long)p->n1 * p->Hc;
+  dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((run + 255) / 256, 64)), (unsigned)(p->nc0 * p->world));
+  slab_push_kernel<<<grid, 256, 0, st>>>(buf, pp, p->rank, p->n0, k * p->nc0, p->world, p->n1, p->H, p->Hc);
   SBX_CUDA(cudaGetLastError());
   return SBX_OK;
 }
@@ -441,7 +498,30 @@ extern "C" int sbx_scatter_slab_execute(sbx_slab_plan* p, const double* local_sl
     if (p->timed) cudaEventRecord(p->ev[4], st);
     return SBX_OK;
   }
-  if (p->timed || p->world == 1) {
+  if (p->p2p && p->world > 1) {
+    if (p->timed) {
+      // serial form for stage timing: [transform + push of every chunk] [barrier] ...
+      for (int k = 0; k < p->K; ++k) {
+        if ((rc = slab_fft_chunk(p, local_slab, k, p->d_f, st))) return rc;
+        if ((rc = slab_push(p, k, p->d_f, st))) return rc;
+      }
+      cudaEventRecord(p->ev[1], st);
+    } else {
+      // chunk k is pushed into the peers on s_comm while chunk k + 1 is transformed on the caller's stream
+      for (int k = 0; k < p->K; ++k) {
+        double2* buf = (k & 1) ? p->d_f2 : p->d_f;
+        if (k >= 2) SBX_CUDA(cudaStreamWaitEvent(st, p->ev_push[k - 2], 0));  // the buffer's previous push has read it
+        if ((rc = slab_fft_chunk(p, local_slab, k, buf, st))) return rc;
+        SBX_CUDA(cudaEventRecord(p->ev_chunk[k], st));
+        SBX_CUDA(cudaStreamWaitEvent(p->s_comm, p->ev_chunk[k], 0));
+        if ((rc = slab_push(p, k, buf, p->s_comm))) return rc;
+        SBX_CUDA(cudaEventRecord(p->ev_push[k], p->s_comm));
+      }
+      for (int k = std::max(0, p->K - 2); k < p->K; ++k) SBX_CUDA(cudaStreamWaitEvent(st, p->ev_push[k], 0));
+    }
+    // every rank's pieces have landed in every d_x once all ranks have passed this point
+    SBX_NCCL(g_nccl.AllReduce(p->d_flag, p->d_flag, 1, ncclInt, ncclSum, p->comm, st));
+  } else if (p->timed || p->world == 1) {
     // serial form (stage timing; or nothing to exchange): all chunks through stage A, then all exchanges
     for (int k = 0; k < p->K; ++k)
       if ((rc = slab_stage_a(p, local_slab, k, st))) return rc;
@@ -467,6 +547,52 @@ extern "C" int sbx_scatter_slab_execute(sbx_slab_plan* p, const double* local_sl
   if (p->timed) cudaEventRecord(p->ev[4], st);
   return SBX_OK;
 }
+
+extern "C" int sbx_scatter_slab_ipc_export(sbx_slab_plan* p, void* handle_host) {
+  if (!p || !handle_host) return fail(SBX_EINVAL, "NULL argument");
+  static_assert(sizeof(cudaIpcMemHandle_t) == SBX_IPC_HANDLE_BYTES, "cudaIpcMemHandle_t size");
+  if (p->pruned || p->world < 2 || !p->d_x) { memset(handle_host, 0, SBX_IPC_HANDLE_BYTES); return SBX_OK; }  // nothing to map
+  DeviceGuard guard(p->device);
+  cudaIpcMemHandle_t h;
+  SBX_CUDA(cudaIpcGetMemHandle(&h, p->d_x));
+  memcpy(handle_host, &h, sizeof(h));
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_slab_ipc_attach(sbx_slab_plan* p, const void* handles_host) {
+  if (!p || !handles_host) return fail(SBX_EINVAL, "NULL argument");
+  if (p->pruned || p->world < 2) return SBX_OK;  // pruned mode has no exchange
+  if (p->world > 16) return fail(SBX_EINVAL, "the fused exchange supports up to 16 ranks, got %d", p->world);
+  if (!p->d_f2) return fail(SBX_EINVAL, "plan has no second chunk buffer");
+  DeviceGuard guard(p->device);
+  for (int r = 0; r < p->world; ++r) {
+    if (r == p->rank) { p->peer_x[r] = p->d_x; continue; }
+    cudaIpcMemHandle_t h;
+    memcpy(&h, (const char*)handles_host + (size_t)r * SBX_IPC_HANDLE_BYTES, sizeof(h));
+    void* ptr = nullptr;
+    const cudaError_t e = cudaIpcOpenMemHandle(&ptr, h, cudaIpcMemLazyEnablePeerAccess);
+    if (e != cudaSuccess) {
+      for (int q = 0; q < r; ++q) if (p->peer_open[q]) { cudaIpcCloseMemHandle(p->peer_x[q]); p->peer_open[q] = false; }
+      return fail(SBX_ECUDA, "cudaIpcOpenMemHandle(rank %d): %s", r, cudaGetErrorString(e));
+    }
+    p->peer_x[r] = (double2*)ptr;
+    p->peer_open[r] = true;
+  }
+  p->p2p = true;
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_slab_ipc_detach(sbx_slab_plan* p) {
+  if (!p) return SBX_OK;
+  DeviceGuard guard(p->device);
+  cudaDeviceSynchronize();
+  for (int r = 0; r < 16; ++r)
+    if (p->peer_open[r]) { cudaIpcCloseMemHandle(p->peer_x[r]); p->peer_open[r] = false; p->peer_x[r] = nullptr; }
+  p->p2p = false;
+  return SBX_OK;
+}
+
+extern "C" int sbx_scatter_slab_exchange(const sbx_slab_plan* p) { return !p ? SBX_EINVAL : (p->pruned ? 0 : (p->p2p ? 2 : 1)); }
 
 extern "C" const char* sbx_scatter_slab_kernel(const sbx_slab_plan* p) {
   return p && p->inner ? sbx_scatter_plan_kernel(p->inner) : "";

@@ -208,6 +208,24 @@ class SlabScatter:
         self.planes = slab_planes(self.N[0], self.rank, self.world)
         # 4: pruned DFT (mode sums + one small all-reduce); 1: slab FFT with all-to-all.  SBX_SLAB_PATH=fft|pruned forces one.
         self.path = int(L_.sbx_scatter_slab_path(self._h))
+        # slab FFT mode: map every rank's receive buffer (CUDA IPC) so that the pack kernel stores straight into the
+        # peers over NVLink (fused pack + exchange).  All ranks must agree: if the mapping fails anywhere, every rank
+        # detaches and the NCCL send/recv exchange is used.  SBX_SLAB_EXCHANGE=nccl skips the attempt.
+        if self.world > 1 and self.path != _lib.PATH_PRUNED_FUSED and os.environ.get("SBX_SLAB_EXCHANGE", "p2p") != "nccl":
+            hb = (C.c_char * 64)()
+            ok = L_.sbx_scatter_slab_ipc_export(self._h, hb) == 0
+            blobs = [None] * self.world
+            dist.all_gather_object(blobs, bytes(hb.raw) if ok else None)
+            if all(b is not None for b in blobs):
+                allh = (C.c_char * (64 * self.world)).from_buffer_copy(b"".join(blobs))
+                ok = L_.sbx_scatter_slab_ipc_attach(self._h, allh) == 0
+            else:
+                ok = False
+            flag = torch.tensor([1 if ok else 0], device=torch.device("cuda", self.device), dtype=torch.int32)
+            dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+            if int(flag.item()) == 0:
+                L_.sbx_scatter_slab_ipc_detach(self._h)
+        self.exchange = {0: "none", 1: "nccl_send_recv", 2: "p2p_fused"}.get(int(L_.sbx_scatter_slab_exchange(self._h)), "?")
 
     @property
     def kernel(self) -> str:
@@ -249,6 +267,17 @@ class SlabScatter:
     def close(self):
         L_ = _lib.lib()
         if self._h:
+            if getattr(self, "exchange", "") == "p2p_fused":
+                # unmap the peers' buffers on every rank before any rank frees its own (the exporter must outlive the mappings)
+                L_.sbx_scatter_slab_ipc_detach(self._h)
+                try:
+                    import torch.distributed as dist
+
+                    if dist.is_available() and dist.is_initialized():
+                        dist.barrier()
+                except Exception:
+                    pass
+                self.exchange = "nccl_send_recv"
             L_.sbx_scatter_slab_plan_destroy(self._h)
             self._h = C.c_void_p()
         if self._comm:

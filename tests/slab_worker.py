@@ -28,6 +28,8 @@ def main():
     mat = synth.field_numpy(5, (n, n, n), cells=2)
     L = synth.box_for(2)
     slab = D.SlabScatter((n, n, n), L, cutoff=args.cutoff, device=local)
+    want = os.environ.get("SBX_EXPECT_EXCHANGE")
+    assert not want or slab.exchange == want, f"exchange is {slab.exchange}, expected {want}"
     lo, hi = slab.planes
     local_slab = torch.from_numpy(np.ascontiguousarray(mat[lo:hi])).cuda(local)
     qI = slab.q_intensity(local_slab)
@@ -44,7 +46,7 @@ def main():
         assert np.array_equal(qI[:, 0], ref[:, 0])
         tol = 1e-9 * np.abs(ref[:-1, 1]) + 1e-12 * np.abs(ref[:, 1]).max()
         assert np.all(np.abs(qI[:-1, 1] - ref[:-1, 1]) <= tol), "slab shell sums differ from the oracle"
-        print(f"slab parity ok: {world} ranks, {n}^3")
+        print(f"slab parity ok: {world} ranks, {n}^3, exchange {slab.exchange}")
     slab.close()
     dist.destroy_process_group()
 

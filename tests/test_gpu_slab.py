@@ -100,18 +100,22 @@ def test_slab_rejects_bad_partition(sbx_lib):
     assert ei.value.code == -1
 
 
-@pytest.mark.parametrize("slab_path,extra", [("fft", {}), ("pruned", {}), ("fft", {"SBX_SLAB_CHUNKS": "8", "SBX_SLAB_ALLCOLS": "1"}),
-                                             ("fft", {"SBX_SLAB_CHUNKS": "1"})])
-def test_nccl_slab_two_ranks(slab_path, extra):
-    """The real NCCL path, one process per GPU: slab FFT (chunked all-to-all on its own stream overlapping the 2D
-    transforms, + all-reduce; also with 8 chunks and every column exchanged, and unchunked) and pruned mode
-    (all-reduce only)."""
+@pytest.mark.parametrize("port,slab_path,extra", [
+    (29517, "fft", {"SBX_EXPECT_EXCHANGE": "p2p_fused"}), (29518, "pruned", {"SBX_EXPECT_EXCHANGE": "none"}),
+    (29519, "fft", {"SBX_SLAB_CHUNKS": "8", "SBX_SLAB_ALLCOLS": "1", "SBX_EXPECT_EXCHANGE": "p2p_fused"}),
+    (29520, "fft", {"SBX_SLAB_CHUNKS": "1", "SBX_EXPECT_EXCHANGE": "p2p_fused"}),
+    (29521, "fft", {"SBX_SLAB_EXCHANGE": "nccl", "SBX_EXPECT_EXCHANGE": "nccl_send_recv"}),
+    (29522, "fft", {"SBX_SLAB_EXCHANGE": "nccl", "SBX_SLAB_CHUNKS": "8", "SBX_SLAB_ALLCOLS": "1", "SBX_EXPECT_EXCHANGE": "nccl_send_recv"})])
+def test_nccl_slab_two_ranks(port, slab_path, extra):
+    """The real multi-process path, one process per GPU.  Slab FFT mode with the fused pack + exchange over peer memory
+    (default: CUDA IPC-mapped receive buffers, chunk pushes on a second stream overlapping the 2D transforms; also with 8
+    chunks and every column exchanged, and unchunked), the same with the NCCL send/recv exchange, and pruned mode
+    (all-reduce only).  The worker asserts which exchange the plan ended up with."""
     import torch
 
     if torch.cuda.device_count() < 2:
         pytest.skip("needs >= 2 GPUs (the single-GPU emulation test covers the decomposition)")
     world = 2
-    port = 29517 + ["fft", "pruned"].index(slab_path) + 2 * len(extra)
     cmd = [sys.executable, "-m", "torch.distributed.run", "--nnodes=1", f"--nproc-per-node={world}", "--master-addr", "127.0.0.1",
            "--master-port", str(port), str(ROOT / "tests" / "slab_worker.py"), "--grid", "64"]
     res = subprocess.run(cmd, capture_output=True, text=True, timeout=600, cwd=str(ROOT), env=dict(os.environ, SBX_SLAB_PATH=slab_path, **extra))
