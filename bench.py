@@ -544,17 +544,19 @@ def run_slab(args, modes=("pruned", "fft")):
     for x0 in range(lo, hi, 32):
         x1 = min(hi, x0 + 32)
         local_slab[x0 - lo:x1 - lo] = synth.field_planes_torch(3, (n, n, n), x0, x1, cells=args.cells, device=dev)
+    # "fft" runs the default exchange (fused pack + push into the peers' buffers over NVLink when CUDA IPC maps them,
+    # else NCCL send/recv).  The other variants are the exchange-bound form of the mode, where every column of the half
+    # spectrum travels (what a cutoff reaching the Nyquist column needs): fused / NCCL chunked / NCCL unchunked.
+    variants = {"pruned": ("pruned", {}), "fft": ("fft", {}), "fft_allcols": ("fft", {"SBX_SLAB_ALLCOLS": "1"}),
+                "fft_allcols_nccl": ("fft", {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_EXCHANGE": "nccl"}),
+                "fft_allcols_nccl_unchunked": ("fft", {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_EXCHANGE": "nccl", "SBX_SLAB_CHUNKS": "1"})}
+    names = list(modes) + ([v for v in variants if v.startswith("fft_allcols")] if "fft" in modes and world > 1 else [])
+    if getattr(args, "slab_variants", ""):
+        names = [v for v in args.slab_variants.split(",") if v in variants]
+    modes = tuple(names)
     recs, rows = {}, {}
-    for mode in modes:
-        recs[mode], rows[mode], q = _slab_mode(args, mode, local_slab, ctx)
-    if "fft" in modes and world > 1:
-        # "fft" above runs the default exchange (fused pack + push into the peers' buffers over NVLink when CUDA IPC maps
-        # them, else NCCL send/recv).  Variants: the exchange-bound form of the mode, where every column of the half
-        # spectrum travels (what a cutoff reaching the Nyquist column needs): fused / NCCL chunked / NCCL unchunked.
-        for name, env in (("fft_allcols", {"SBX_SLAB_ALLCOLS": "1"}),
-                          ("fft_allcols_nccl", {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_EXCHANGE": "nccl"}),
-                          ("fft_allcols_nccl_unchunked", {"SBX_SLAB_ALLCOLS": "1", "SBX_SLAB_EXCHANGE": "nccl", "SBX_SLAB_CHUNKS": "1"})):
-            recs[name], rows[name], q = _slab_mode(args, "fft", local_slab, ctx, env)
+    for name in names:
+        recs[name], rows[name], q = _slab_mode(args, variants[name][0], local_slab, ctx, variants[name][1])
     del local_slab
     torch.cuda.empty_cache()
     if rank != 0:
@@ -774,6 +776,7 @@ def main():
     ap.add_argument("--cpu-voxels", type=int, default=4096)
     ap.add_argument("--sweep-fields", type=int, default=256, help="256^3 fields per GPU of the sweep record (config 4: 2048 over 8 GPUs)")
     ap.add_argument("--slab-grid", type=int, default=1024, help="grid of the one-field slab record (config 5)")
+    ap.add_argument("--slab-variants", default="", help="--workload slab: comma list of pruned,fft,fft_allcols,fft_allcols_nccl,fft_allcols_nccl_unchunked")
     ap.add_argument("--sub", default="all", help="sub-records of the default line: all | none | comma list of voronoi,sweep,slab,voronoi_sharded")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup

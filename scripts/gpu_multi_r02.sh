@@ -2,7 +2,7 @@
 # r02: N-GPU run (N = $1): NCCL slab tests, then the driver-style bench line with slab / sharded / sweep sub-records
 N=${1:-2}
 mkdir -p gpurun_out/r02
-python -m pytest tests/test_gpu_slab.py -m gpu -x -q 2>&1 | tail -5 > gpurun_out/r02/pytest_slab_n$N.txt; cat gpurun_out/r02/pytest_slab_n$N.txt
+if [ -z "$SKIP_TESTS" ]; then python -m pytest tests/test_gpu_slab.py -m gpu -x -q 2>&1 | tail -5 > gpurun_out/r02/pytest_slab_n$N.txt; cat gpurun_out/r02/pytest_slab_n$N.txt; fi
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29531 bench.py --gpus $N --steps 20 --warmup 3 > gpurun_out/r02/bench_default_n$N.json 2> gpurun_out/r02/bench_default_n$N.err; echo "bench rc $?"; tail -c 800 gpurun_out/r02/bench_default_n$N.err
 python - <<PY
 import json

@@ -122,15 +122,40 @@ slab_pack_kernel(const double2* __restrict__ F, double2* __restrict__ Y, int n0,
 // Fused pack + exchange: like slab_pack_kernel, but piece d goes straight into rank d's receive buffer
 // X_d[(sender*n0 + x0 + xl)][jl][c < Hc] (peer memory mapped through CUDA IPC; the own piece is local).
 struct PeerPtrs { double2* x[16]; };
-__global__ void __launch_bounds__(256)
-slab_push_kernel(const double2* __restrict__ F, PeerPtrs peers, int sender, int n0, int x0, int P, int n1, int H, int Hc) {
-  const int xl = blockIdx.y / P, d = blockIdx.y - xl * P;
+// PERSISTENT grid of a few CTAs (enough to saturate NVLink, SBX_SLAB_PUSH_CTAS, default 32): the kernel shares the GPU
+// with the cuFFT passes of the next chunk, and a grid that filled every SM would simply run before or after them.
+// Work item = (plane xl of the chunk, destination d, 4096-element segment of the n1 x Hc run), remote destinations
+// first in rotated order so that the ranks do not all write to the same peer at once.
+__global__ void __launch_bounds__(512)
+slab_push_kernel(const double2* __restrict__ F, PeerPtrs peers, int sender, int n0, int x0, int nc0, int P, int n1, int H, int Hc) {
   const long long run = (long long)n1 * Hc;
-  const double2* src = F + ((long long)xl * P + d) * n1 * H;
-  double2* dst = peers.x[d] + ((long long)sender * n0 + x0 + xl) * run;
-  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < run; i += (long long)gridDim.x * blockDim.x) {
-    const long long jl = i / Hc;
-    dst[i] = src[jl * H + (i - jl * Hc)];
+  constexpr int kSeg = 4096;  // = blockDim.x * kU below
+  const int segs = (int)((run + kSeg - 1) / kSeg);
+  const long long items = (long long)nc0 * P * segs;
+  for (long long it = blockIdx.x; it < items; it += gridDim.x) {
+    const int seg = (int)(it % segs);
+    const long long pd = it / segs;
+    const int xl = (int)(pd % nc0);
+    const int d = (sender + 1 + (int)(pd / nc0)) % P;  // own piece last
+    const double2* src = F + ((long long)xl * P + d) * n1 * H;
+    double2* dst = peers.x[d] + ((long long)sender * n0 + x0 + xl) * run;
+    const long long i0 = (long long)seg * kSeg, i1 = min(run, i0 + kSeg);
+    // kU independent 16-byte loads in flight per thread before the stores: a few CTAs have to cover ~2 us of NVLink
+    // latency (one load -> store pair per thread gave 13 GB/s per CTA)
+    constexpr int kU = 8;  // 512 threads x 8 = one 4096-element segment (64 KB) per pass
+    double2 v[kU];
+    long long idx[kU];
+#pragma unroll
+    for (int u = 0; u < kU; ++u) {
+      idx[u] = i0 + threadIdx.x + (long long)u * blockDim.x;
+      if (idx[u] < i1) {
+        const long long jl = idx[u] / Hc;
+        v[u] = __ldcs(src + jl * H + (idx[u] - jl * Hc));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < kU; ++u)
+      if (idx[u] < i1) dst[idx[u]] = v[u];
   }
   __threadfence_system();  // the stores to peer memory are performed before the kernel counts as complete
 }
@@ -170,6 +195,7 @@ struct sbx_slab_plan {
   bool peer_open[16] = {};
   cudaEvent_t ev_push[16] = {};
   int* d_flag = nullptr;                   // operand of the barrier all-reduce
+  int push_ctas = 48;                      // persistent grid of slab_push_kernel
   double *d_rep = nullptr, *d_kvlast = nullptr, *d_partial = nullptr;
   double2* d_plane2 = nullptr;
   int blocks = 1;
@@ -327,7 +353,12 @@ static int slab_build(sbx_slab_plan** out, ncclComm_t comm, int rank, int world,
   if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_y, spec_bytes);
   if (e == cudaSuccess) e = cudaMalloc((void**)&p->d_partial, (size_t)sh.n_shells * sizeof(double));
   for (int i = 0; i < 5 && e == cudaSuccess; ++i) e = cudaEventCreate(&p->ev[i]);
-  if (e == cudaSuccess) e = cudaStreamCreateWithFlags(&p->s_comm, cudaStreamNonBlocking);
+  if (e == cudaSuccess) {  // exchange stream at the highest priority: its few CTAs are placed as soon as an SM has room
+    int lo_pri = 0, hi_pri = 0;
+    cudaDeviceGetStreamPriorityRange(&lo_pri, &hi_pri);
+    e = cudaStreamCreateWithPriority(&p->s_comm, cudaStreamNonBlocking, hi_pri);
+  }
+  { const char* pc = getenv("SBX_SLAB_PUSH_CTAS"); if (pc && atoi(pc) > 0) p->push_ctas = std::min(atoi(pc), 4096); }
   for (int i = 0; i < p->K && e == cudaSuccess; ++i) e = cudaEventCreateWithFlags(&p->ev_chunk[i], cudaEventDisableTiming);
   if (e == cudaSuccess) e = cudaEventCreateWithFlags(&p->ev_comm, cudaEventDisableTiming);
   if (e == cudaSuccess && world > 1 && world <= 16) {
@@ -387,9 +418,7 @@ static int slab_fft_chunk(sbx_slab_plan* p, const double* local_slab, int k, dou
 static int slab_push(sbx_slab_plan* p, int k, const double2* buf, cudaStream_t st) {
   PeerPtrs pp;
   for (int r = 0; r < 16; ++r) pp.x[r] = r < p->world ? p->peer_x[r] : nullptr;
-  const long long run = (long long)p->n1 * p->Hc;
-  dim3 grid((unsigned)std::max<long long>(1, std::min<long long>((run + 255) / 256, 64)), (unsigned)(p->nc0 * p->world));
-  slab_push_kernel<<<grid, 256, 0, st>>>(buf, pp, p->rank, p->n0, k * p->nc0, p->world, p->n1, p->H, p->Hc);
+  slab_push_kernel<<<p->push_ctas, 512, 0, st>>>(buf, pp, p->rank, p->n0, k * p->nc0, p->nc0, p->world, p->n1, p->H, p->Hc);
   SBX_CUDA(cudaGetLastError());
   return SBX_OK;
 }
