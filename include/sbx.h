@@ -160,6 +160,9 @@ int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* plan, const double* seeds, 
                                    const double* weights, int mode, const double* box_host,
                                    const uint8_t* mask, int32_t* labels, int64_t x_lo, int64_t x_hi,
                                    void* stream, int64_t* stats_host);
+/* which kernels the last execute of this plan ran (introspection for tests and bench records; no reference
+ * counterpart): 0 = tile path (coarse + mid + label kernels), 1 = cell-list path, -1 = no execute yet */
+int sbx_voronoi_plan_last_path(const sbx_voronoi_plan* plan);
 int sbx_voronoi_plan_destroy(sbx_voronoi_plan* plan);
 /* Allocation-free labelling.  NO COUNTERPART IN THE REFERENCE: added for callers
  * that cannot call cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it).  Same result as

@@ -52,6 +52,7 @@ _SIGNATURES = {
     "sbx_voronoi_plan_create": (C.c_int, [C.POINTER(_vp), C.c_int, C.c_int, _i64p]),
     "sbx_voronoi_plan_execute": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, _f64p, _vp, _vp, _vp, _i64p]),
     "sbx_voronoi_plan_execute_range": (C.c_int, [_vp, _vp, C.c_int64, _vp, C.c_int, _f64p, _vp, _vp, C.c_int64, C.c_int64, _vp, _i64p]),
+    "sbx_voronoi_plan_last_path": (C.c_int, [_vp]),
     "sbx_voronoi_plan_destroy": (C.c_int, [_vp]),
     "sbx_voronoi_label_noalloc": (C.c_int, [C.c_int, C.c_int, _i64p, _vp, C.c_int64, _f64p, _vp, _vp, C.c_int64, C.c_int64, _vp]),
     "sbx_scatter_slab_plan_create": (C.c_int, [C.POINTER(_vp), _vp, C.c_int, C.c_int, C.c_int, _i64p, _f64p, C.c_int, C.c_double]),

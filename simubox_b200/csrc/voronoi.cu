@@ -873,6 +873,7 @@ struct sbx_voronoi_plan {
   SeedRec* pts = nullptr;
   long long cell_cap = 0, pts_cap = 0;
   int cell_ncell = -1;
+  int last_path = -1;  // 0 tile path (coarse + mid + label), 1 cell-list path
   // tile path on a plane range: full-grid scratch
   int32_t* tmp_labels = nullptr;
   uint8_t* tmp_mask = nullptr;
@@ -1094,6 +1095,7 @@ extern "C" int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* p, const double*
     CellGeo c{};
     cell_geometry(p, g, S, (int)x_lo, (int)x_hi, c);
     if (c.nt[0] > 65535 || c.nt[1] > 65535) return fail(SBX_EINVAL, "grid too large for the cell path");
+    p->last_path = 1;
     int rc = ensure_cell_workspace(p, c, st);
     if (rc) return rc;
     if (p->ndim == 3) {
@@ -1104,6 +1106,7 @@ extern "C" int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* p, const double*
       else launch_cells<2, false>(c, seeds, p->cell_count, p->cell_start, p->pts, mask, labels, stats, st);
     }
   } else {
+    p->last_path = 0;
     int rc = ensure_tile_workspace(p);
     if (rc) return rc;
     const size_t plane = (size_t)(p->ndim == 3 ? (long long)g.N[1] * g.N[2] : (long long)g.N[2]);
@@ -1143,6 +1146,8 @@ extern "C" int sbx_voronoi_plan_execute_range(sbx_voronoi_plan* p, const double*
   }
   return SBX_OK;
 }
+
+extern "C" int sbx_voronoi_plan_last_path(const sbx_voronoi_plan* p) { return p ? p->last_path : SBX_EINVAL; }
 
 extern "C" int sbx_voronoi_plan_execute(sbx_voronoi_plan* p, const double* seeds, int64_t S, const double* weights,
                                         int mode, const double* box_host, const uint8_t* mask, int32_t* labels,

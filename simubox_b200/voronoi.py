@@ -136,7 +136,8 @@ class VoronoiCell:
             st_arr.ctypes.data_as(C.POINTER(C.c_int64)) if stats else None))
         out = labels if return_tensor else labels.cpu().numpy()
         if stats:
-            return out, dict(evaluations=int(st_arr[0]), tiles=int(st_arr[1]), overflow_tiles=int(st_arr[2]))
+            path = {0: "tiles", 1: "cells"}.get(int(_lib.lib().sbx_voronoi_plan_last_path(plan._h)), "?")
+            return out, dict(evaluations=int(st_arr[0]), tiles=int(st_arr[1]), overflow_tiles=int(st_arr[2]), path=path)
         return out
 
     @classmethod

@@ -195,7 +195,7 @@ def test_cell_path_ranges_match_oracle(sbx_lib, shape, S, periodic, masked):
         parts = [VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, planes=sp) for sp in spans if sp[1] > sp[0]]
         assert np.array_equal(np.concatenate(parts, axis=0), ref), f"world {world}"
     lab, st = VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, planes=(0, shape[0] - 1), stats=True)
-    assert np.array_equal(lab, ref[:-1]) and st["tiles"] > 0
+    assert np.array_equal(lab, ref[:-1]) and st["tiles"] > 0 and st["path"] == "cells"
 
 
 def test_cell_path_exact_ties_and_clusters(sbx_lib):
@@ -229,3 +229,27 @@ def test_cell_path_256_cubed_slabs_equal_whole_grid(sbx_lib):
     for lo in range(0, 256, 32):
         part = VoronoiCell.label_grid(pts, 0, shape=shape, box=box, mask=mask, return_tensor=True, planes=(lo, lo + 32))
         assert torch.equal(part, whole[lo:lo + 32])
+
+
+@pytest.mark.parametrize("shape,S,periodic,want", [((64, 64, 64), 64, False, "tiles"), ((64, 64, 64), 600, True, "cells"),
+                                                   ((48, 48, 48), 13000, False, "cells"), ((96, 96), 40, True, "tiles")])
+def test_automatic_path_choice_and_agreement(sbx_lib, shape, S, periodic, want):
+    """Whole grids: the tile path for sparse, few seeds (spacing >= 11 voxels, fewer than 12000 seeds), the cell-list
+    path otherwise (dense seedings overflow the tile path's staging and took its full-scan fallback in r01);
+    sbx_voronoi_plan_last_path reports which one ran.  Whatever was chosen must equal the oracle and the same grid
+    labelled in plane ranges (always the cell path)."""
+    from simubox_b200 import VoronoiCell
+    from simubox_b200.distributed import shard_range
+
+    rng = np.random.default_rng(S + len(shape))
+    pts = rng.uniform(0, 1, (S, len(shape))) * np.array(shape)
+    box = tuple(float(n) for n in shape) if periodic else None
+    lab, st = VoronoiCell.label_grid(pts, 0, shape=shape, box=box, stats=True)
+    assert st["path"] == want, st
+    parts = [VoronoiCell.label_grid(pts, 0, shape=shape, box=box, planes=shard_range(shape[0], r, 3)) for r in range(3)]
+    assert np.array_equal(np.concatenate(parts, axis=0), lab)
+    if want == "tiles":
+        assert np.array_equal(lab, voronoi_np.label_grid(pts, 0, shape, box=box))
+    else:
+        vox = np.stack([rng.integers(0, n, 4096) for n in shape], axis=1)
+        assert np.array_equal(lab[tuple(vox.T)], voronoi_np.label_voxels(pts, 0, vox, box=box, chunk=64))
