@@ -472,7 +472,7 @@ def run_voronoi(args):
                      "unit": "GB/s", "frac": achieved / peak, "traffic": measured_traffic(f"coarse_kernel+mid_kernel+label_kernel|{n}^3|{S} seeds"),
                      "peak_source": peak_src,
                      "algorithmic_bytes_per_grid": unit_bytes, "evaluations_per_live_voxel": st["evaluations"] / max(live, 1),
-                     "overflow_tiles": st["overflow_tiles"],
+                     "overflow_tiles": st["overflow_tiles"], "path": st.get("path"),
                      "note": "issue/latency bound, not HBM bound (DESIGN.md section 4): three launches, fp64 argmin over ~3.3 candidates per voxel"},
         "cpu_baseline": {"value": cpu_rate, "unit": "voxels/s", "cores": cores, "kind": "port",
                          "sample": f"{args.cpu_voxels} random voxels of the same grid through oracle/voronoi_np.label_voxels (27 images x {S} seeds per voxel)"},
