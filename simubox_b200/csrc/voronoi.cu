@@ -2,8 +2,11 @@
 //
 // Replaces the per-pixel Python loop of VoronoiCell.weighted_voronoi_diagrams
 // (SimuBox/calculator/voronoi.py:284-292) with VoronoiCell.additive (:244-246) or
-// VoronoiCell.power (:249-255) as the distance.  The grid is always handled as three internal
-// axes (a 2D image is 1 x X x Y); three kernels:
+// VoronoiCell.power (:249-255) as the distance.  Two paths behind one plan (the host code at the end of this file
+// chooses: sbx_voronoi_plan_execute_range): the TILE path below (any mode, weights; whole grids with sparse, few
+// seeds) and the CELL-LIST path of voronoi_cells.cuh (additive, no weights: plane ranges, dense or many seeds,
+// sbx_voronoi_label_noalloc).  The grid is always handled as three internal
+// axes (a 2D image is 1 x X x Y); the tile path is three kernels:
 //   1. coarse_kernel: per COARSE tile (32^3 voxels / 256^2 pixels) the seeds that can win anywhere
 //      inside it, out of all S seeds (interval bounds with slack, ascending seed index);
 //   2. mid_kernel: one warp per MID tile (16^3 / 64^2) filters its parent's list and writes staged

@@ -1,6 +1,8 @@
-// voronoi_cells.cuh -- cell-list labelling path (additive distance, no weights): the default for
-// VoronoiCell.weighted_voronoi_diagrams' per-pixel loop (SimuBox/calculator/voronoi.py:284-292 with
-// VoronoiCell.additive, :244-246, weights == 0).  Included by voronoi.cu.
+// voronoi_cells.cuh -- cell-list labelling path (additive distance, no weights) for the per-pixel loop of
+// VoronoiCell.weighted_voronoi_diagrams (SimuBox/calculator/voronoi.py:284-292 with VoronoiCell.additive, :244-246,
+// weights == 0).  Included by voronoi.cu, which chooses between this path and the tile path (coarse / mid / label
+// kernels): plane ranges of a grid sharded across GPUs, dense or many seeds, and the allocation-free entry point run
+// here; whole grids with sparse, few seeds run the tile path (measurements: DESIGN.md section 4a).
 //
 // Periodicity in the reference is "replicate every seed into its 3^d images p + m L and take the argmin"
 // (SURVEY.md 8c).  Here the images are made explicit once: every (seed, image) whose image can be the nearest
@@ -14,24 +16,26 @@
 //                          row start + counts of the cells before it in its row + a per-cell cursor.  The CTAs
 //                          also write the per-cell `start` table the label kernel reads.
 //   3. label_cells_kernel  one WARP per gather tile (8 x 8 x 16 voxels / 32 x 32 pixels), no CTA-level barrier;
-//                          its CTAs also zero the counters for the next labelling.
+//                          on their way out its threads zero the counters for the next labelling.
 //                          Cells are C-ordered, so all points of the cells [cl2, ch2] of one (c0, c1) row are
 //                          one contiguous range: the warp reads the ranges of the rows that intersect
-//                          tile +- R and stages every point as (fp32 offset from the tile centre, seed index).
-//                          A = the point nearest to the centre; if R does not cover sqrt(max_x d_A^2) the search
-//                          is repeated with that radius.  Points whose bisector with A misses the tile are
-//                          dropped (d_B^2 - d_A^2 is affine in x: its minimum over a box sits on a corner); each
-//                          half tile (4 x 8 x 8 / 32 x 8) repeats that against its own nearest point.  These
-//                          tests only have to be CONSERVATIVE, so they run in fp32 with a margin that bounds
-//                          their rounding.  Evaluation: a lane owns a column of 8 voxels and tracks, per voxel,
-//                          the smallest and second smallest fp32 squared distance with the candidate number in
-//                          the low mantissa bits (FADD, LOP3, 3 x VIMNMX per voxel and candidate).  A voxel whose
-//                          two smallest differ by more than the certified fp32 error bound has its reference
-//                          label; the columns that hold any other voxel (near ties, 1e-4 of them on random
-//                          seeds, every cell face on a lattice) are redone with the reference's fp64 expression,
+//                          tile +- R and stages the fp64 records of the points within R of the tile's box (cells
+//                          overhang the box; a point farther than R on some axis is farther than R from every
+//                          voxel).  A = the point nearest to the tile centre; if R does not cover the farthest
+//                          voxel's distance to A the search is repeated with that radius.
+//                          Pruning and evaluation use g_c(x) = d_c^2(x) - d_A^2(x), which is AFFINE in x: its four
+//                          coefficients are formed in fp64, its minimum over a box is a closed form, so "can c beat
+//                          A anywhere in the box" is exact up to a 1e-9 margin (tile level, then once more per half
+//                          tile of 4 x 8 x 8 / 32 x 8 voxels against the half's own nearest point).
+//                          Evaluation: a lane owns a column of 8 voxels; per candidate one fp32 FMA per voxel
+//                          gives g_c, and the smallest and second smallest are tracked as integer keys with the
+//                          candidate number in the low mantissa bits (FFMA, LOP3, 3 x VIMNMX per voxel and
+//                          candidate).  A voxel whose two smallest differ by more than the certified fp32 error
+//                          has the reference's label; a column holding any other voxel (near ties: ~1e-4 on random
+//                          seeds, every cell face on a lattice) is redone with the reference's fp64 expression,
 //                          rounded roots compared, equal roots to the lower seed index (np.argmin).
-// A tile whose search box holds more than kStage image points is labelled by a direct scan of the box (exact,
-// slow; counted in stats[2]).
+// A tile whose search box holds more than kStage points within R is labelled by a direct scan of the box's cells
+// (exact, slow; counted in stats[2]).
 #pragma once
 
 namespace sbx {
