@@ -46,11 +46,13 @@ class _VoronoiPlan:
             pass
 
 
-def _get_plan(device: int, shape) -> _VoronoiPlan:
-    key = (int(device), tuple(shape))
+def _get_plan(device: int, shape, slot: int = 0) -> _VoronoiPlan:
+    """Cached plan (workspace) per device, grid and ``slot``.  A plan serves one stream at a time; labellings issued
+    on several streams at once must use different slots."""
+    key = (int(device), tuple(shape), int(slot))
     plan = _PLANS.get(key)
     if plan is None:
-        if len(_PLANS) >= 8:
+        if len(_PLANS) >= 16:
             _PLANS.pop(next(iter(_PLANS))).close()
         plan = _PLANS[key] = _VoronoiPlan(device, shape)
     return plan
@@ -80,7 +82,7 @@ class VoronoiCell:
     def label_grid(cls, points, weights=0, shape: Sequence[int] = (500, 500),
                    method: Union[WeightedMode, str] = WeightedMode.ADDITIVE, box: Optional[Sequence[float]] = None,
                    mask=None, device: int = 0, return_tensor: bool = False, stats: bool = False,
-                   planes: Optional[Tuple[int, int]] = None):
+                   planes: Optional[Tuple[int, int]] = None, plan_slot: int = 0):
         """Label every voxel of ``product(range(shape[0]), range(shape[1])[, range(shape[2])])``
         with the index of the seed minimising ``method`` (first minimum, like ``np.argmin``).
 
@@ -89,8 +91,10 @@ class VoronoiCell:
         ``planes=(x_lo, x_hi)``: label only those planes of the first axis (one rank's slab of a grid
         sharded across GPUs, see ``distributed.label_grid_sharded``); the result then has shape
         ``(x_hi - x_lo, *shape[1:])`` and ``mask`` may be the whole-grid mask or the slab's.
+        ``plan_slot``: the call is asynchronous on the current CUDA stream and uses the workspace of plan number
+        ``plan_slot`` of this grid; labellings in flight on different streams need different slots.
         Returns an int32 array of ``shape`` (numpy, or a CUDA tensor with ``return_tensor``);
-        with ``stats=True`` also a dict(evaluations, tiles, overflow_tiles).
+        with ``stats=True`` also a dict(evaluations, tiles, overflow_tiles, path).
         """
         torch = torch_cuda()
         shape = tuple(int(n) for n in shape)
@@ -130,7 +134,7 @@ class VoronoiCell:
             if len(_keep) != nd:
                 raise ValueError(f"box must have {nd} entries")
         st_arr = np.zeros(3, dtype=np.int64) if stats else None
-        plan = _get_plan(device, shape)
+        plan = _get_plan(device, shape, plan_slot)
         _lib.check(_lib.lib().sbx_voronoi_plan_execute_range(
             plan._h, ptr(pts), S, ptr(w), _mode_id(method), pb, ptr(m), ptr(labels), x_lo, x_hi, stream_ptr(device),
             st_arr.ctypes.data_as(C.POINTER(C.c_int64)) if stats else None))
